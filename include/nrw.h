@@ -1,0 +1,197 @@
+/* nrw.h -- C ABI of libnrw.so, the B200 (sm_100a) random-walk engine that replaces the
+ * conventional-compute (`--run_mode pc`) back end of sandialabs/Neural-Random-Walker.
+ *
+ * The reference is pure Python and has no FFI of its own, so there is no existing binding
+ * to mirror; each entry point below names the reference code it replaces
+ * (paths relative to the reference root).  The Python host layer
+ * (neural-random-walker_b200/nrw/engine.py) binds these with ctypes and is the only
+ * caller; INTEGRATION.md shows the stub a reference maintainer would add.
+ *
+ * Conventions
+ *   - every function returns 0 on success, a negative NRW_E* code on failure and never
+ *     throws; nrw_last_error() returns a thread-local message for the last failure;
+ *   - all pointers in nrw_tables / nrw_walk / nrw_replay are DEVICE pointers owned by the
+ *     caller (PyTorch tensors in the Python host); the library allocates only a few
+ *     hundred bytes of per-handle scratch; functions whose name ends in _host take HOST
+ *     pointers and do their own staging;
+ *   - `stream` is a cudaStream_t passed as void*; NULL means the legacy default stream;
+ *   - nothing here synchronises unless the comment says so.
+ */
+#ifndef NRW_H_
+#define NRW_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NRW_ABI_VERSION 1
+
+#define NRW_OK            0
+#define NRW_EINVAL       -1   /* bad argument / unsupported combination            */
+#define NRW_ECUDA        -2   /* a CUDA runtime call failed (see nrw_last_error)    */
+#define NRW_ENOSPC       -3   /* shared memory / buffer capacity exceeded           */
+
+typedef struct nrw_engine nrw_engine;   /* opaque handle: one per (process, device) */
+
+/* ---- table layouts -------------------------------------------------------------- */
+/* alias_layout values */
+#define NRW_ALIAS_NONE    0
+#define NRW_ALIAS_COMPACT 1   /* rowinfo 8 B/row, alias 8 B/entry (fits shared memory)   */
+#define NRW_ALIAS_WIDE    2   /* rowinfo 16 B/row, alias 16 B/entry (any graph, global)  */
+
+/* COMPACT rowinfo  (uint32 w0, w1):  w0 = off[0:20) | n[20:30) | cls[30:32),  w1 = base
+ *         alias    (uint32 thresh, ab): target = base + ((r1 <= thresh) ? ab & 0xffff : ab >> 16)
+ * WIDE    rowinfo  (uint32 off, n, base, cls)
+ *         alias    (uint32 thresh, a, b, 0): target = base + ((r1 <= thresh) ? a : b)
+ * A row with n == 0 is absorbing: a walker is tallied on arrival and never stepped
+ * (the sink row of fluence_mini_app.py:241,381 and the absorbed state of
+ * simple_flux_miniapp.py:285).  `off` indexes the (de-duplicated) alias pattern. */
+
+typedef struct nrw_tables {
+    int32_t  n_rows;          /* meshSize + 1 (fluence) / 3 (simple_flux)                 */
+    int32_t  n_live;          /* rows < n_live are stepped (meshSize)                     */
+    /* CSR with per-row sequential fp64 prefix sums == non-zeros of
+     * np.cumsum(myQ, axis=1) (fluence_mini_app.py:224).  Needed by the cdf sampler and
+     * by replay; may be NULL for alias-only walks.                                       */
+    const int32_t* indptr;    /* [n_rows + 1]                                             */
+    const int32_t* cols;      /* [nnz]                                                    */
+    const double*  cum;       /* [nnz]                                                    */
+    const uint8_t* node_class;/* [n_rows] source class 0..3 (cdf sampler); may be NULL    */
+    int32_t  alias_layout;    /* NRW_ALIAS_*                                              */
+    int32_t  n_alias;         /* entries in `alias`                                       */
+    const void* rowinfo;      /* [n_rows] per alias_layout                                */
+    const void* alias;        /* [n_alias] per alias_layout                               */
+} nrw_tables;
+
+/* ---- Philox walk (K1) -------------------------------------------------------------- */
+#define NRW_SAMPLER_ALIAS 0   /* O(1) alias draw: slot = mulhi(r0, n), coin = r1          */
+#define NRW_SAMPLER_CDF   1   /* the reference's searchsorted(left) on the fp64 prefix
+                                 sums with u = ((r0>>5)*2^26 + (r1>>6)) / 2^53            */
+
+#define NRW_COUNTER_STEPS     0   /* walker-steps == uniform draws (fluence_mini_app.py:243)   */
+#define NRW_COUNTER_EXITS     1   /* arrivals on absorbing rows                                */
+#define NRW_COUNTER_SURVIVORS 2   /* walkers still alive after step nt-1                       */
+#define NRW_COUNTER_TOVERFLOW 3   /* tallies dropped because t >= t_cap (count_tn only)        */
+#define NRW_COUNTER_WALKERS   4   /* walkers started                                           */
+#define NRW_N_COUNTERS        8
+
+typedef struct nrw_walk {
+    /* walkers: global walker id g in [0, start_prefix[n_starts]); walker g starts on
+     * start_nodes[s] where start_prefix[s] <= g < start_prefix[s+1].  This is the
+     * batched form of `initial_walkers=[[node, M]]` (fluence_mini_app.py:229-231, :401);
+     * the launch walks ids [walker_lo, walker_hi) so ranks can shard by id.            */
+    int32_t  n_starts;
+    const int32_t* start_nodes;     /* [n_starts]                                        */
+    const int64_t* start_prefix;    /* [n_starts + 1]                                    */
+    int64_t  walker_lo, walker_hi;
+    uint64_t seed;                  /* Philox key; counter = (g, step block)             */
+    int32_t  nt;                    /* neuraltime: model steps t = 1 .. nt-1 (:236)      */
+    int32_t  sampler;               /* NRW_SAMPLER_*                                     */
+
+    /* per-start score tally (fused fluence_mini_app.py:428-434): for every step
+     * 1 <= t <= nt-2 that lands on a live node k, the walker's score grows by
+     * llrint(time_weight[t] * class_value[cls(k)])  (time_weight NULL => 1.0, in which
+     * case class_value must hold integers).  score[s] += sum over the start's walkers,
+     * score_sq[s] += sum of squared per-walker scores (for the 3-sigma test).           */
+    int64_t* score;                 /* [n_starts] or NULL                                */
+    double*  score_sq;              /* [n_starts] or NULL                                */
+    double   class_value[4];
+    const double* time_weight;      /* [nt] or NULL                                      */
+
+    /* occupancy histogram over nodes, all starts together, steps 1 <= t <= nt-2
+     * (per-block shared-memory histogram when it fits, merged once per block).          */
+    unsigned long long* node_hist;  /* [n_rows] or NULL                                  */
+
+    /* time-resolved counts == tempdata (fluence_mini_app.py:227,245): group gidx of a
+     * walker is its start index s if count_per_start else 0;
+     * count_tn[(gidx * t_cap + t) * n_rows + k] += 1 for 1 <= t < min(nt, t_cap).
+     * (t = 0 is the initial condition and is filled by nrw_expand_*).                   */
+    uint32_t* count_tn;             /* or NULL                                           */
+    int32_t  t_cap;
+    int32_t  count_per_start;
+
+    unsigned long long* counters;   /* [NRW_N_COUNTERS], accumulated (caller zeroes)     */
+} nrw_walk;
+
+/* ---- replay walk (K2): bit-exact with the reference under its own uniform stream ----- */
+typedef struct nrw_replay {
+    int32_t  n_starts;
+    const int32_t* start_nodes;     /* [n_starts]                                        */
+    const int64_t* start_counts;    /* [n_starts] M per start                            */
+    int32_t  nt;
+    const double* u_stream;         /* the reference's np.random.uniform() values, in draw order */
+    int64_t  u_len;
+    /* events: sparse tempdata, (t, node, count) sorted by (start, t, node)              */
+    int32_t* ev_t; int32_t* ev_node; int64_t* ev_count;
+    int64_t  ev_cap;
+    int64_t* ev_offsets;            /* [n_starts + 1]                                    */
+    uint32_t* scratch;              /* [3 * (n_rows + 1)] zeroed by the caller before the first call */
+    /* state: [0] draws used so far, [1] next start index, [2] next t, [3] status
+     * (0 done, 1 stream exhausted -> refill u_stream from position state[0] and call again,
+     *  2 event capacity exceeded), [4] events written.  Caller zeroes before first call. */
+    int64_t* state;                 /* [8]                                               */
+    int64_t  u_base;                /* stream index of u_stream[0]                       */
+} nrw_replay;
+
+/* ---- API ------------------------------------------------------------------------------ */
+int  nrw_abi_version(void);
+const char* nrw_last_error(void);
+
+int  nrw_create(int device, nrw_engine** out);
+int  nrw_destroy(nrw_engine* e);
+/* number of SMs, max opt-in shared memory per block, of the engine's device */
+int  nrw_device_info(nrw_engine* e, int* n_sms, int* max_smem_bytes);
+
+/* K4: per-row sequential fp64 prefix sums of CSR values
+ * (replaces np.cumsum(myQ, axis=1), fluence_mini_app.py:224).                             */
+int  nrw_build_cum(nrw_engine* e, int32_t n_rows, const int32_t* indptr,
+                   const double* vals, double* cum, void* stream);
+
+/* K1: replaces the loops of run_pc, fluence_mini_app.py:236-245 and
+ * simple_flux_miniapp.py:189-201, for all start nodes of run() at once (:397-407).        */
+int  nrw_walk_philox(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, void* stream);
+/* which kernel variant nrw_walk_philox would launch: writes a short name and the launch
+ * geometry (for bench / profiles); no launch.                                             */
+int  nrw_walk_philox_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w,
+                          char* name, int name_len, int* grid, int* block, int* smem_bytes);
+
+/* K2: same loops, consuming the reference's own uniform stream in the reference's order
+ * (t, node ascending, slot) -- fluence_mini_app.py:236-243, Q5/Q6 of SURVEY.md.           */
+int  nrw_walk_replay(nrw_engine* e, const nrw_tables* t, const nrw_replay* r, void* stream);
+
+/* K3: fluence_mini_app.py:422-438 in the reference's (t, k) order, one start per thread:
+ * out[s] = (sum over events of (((count*tw[t])*v)*src[k])*dt) / M[s], 1 <= t <= nt-2, k < n_live. */
+int  nrw_assemble_events(nrw_engine* e, int32_t n_starts, const int64_t* ev_offsets,
+                         const int32_t* ev_t, const int32_t* ev_node, const int64_t* ev_count,
+                         const double* time_weight, const double* src, double v, double dt,
+                         const int64_t* start_counts, int32_t nt, int32_t n_live,
+                         double* out, void* stream);
+
+/* K5: sparse events / dense uint32 counts -> the dense float64 [n_rows, nt] array that
+ * run_pc returns (fluence_mini_app.py:227,247).  `out` is fully written.                  */
+int  nrw_expand_events(nrw_engine* e, int64_t n_events, const int32_t* ev_t,
+                       const int32_t* ev_node, const int64_t* ev_count,
+                       int32_t n_rows, int32_t nt, double* out, void* stream);
+int  nrw_expand_counts(nrw_engine* e, const uint32_t* count_tn, int32_t t_cap, int32_t n_rows,
+                       int32_t nt, int32_t start_node, int64_t start_count,
+                       double* out, void* stream);
+
+/* End-to-end convenience with HOST buffers (what `bench.py` times as e2e): copies the
+ * compact alias tables and the start list to the device, runs K1 in score mode, copies
+ * score / counters back and synchronises `stream`.                                        */
+int  nrw_fluence_scores_host(nrw_engine* e,
+                             int32_t n_rows, int32_t n_live, int32_t n_alias,
+                             const void* rowinfo_host, const void* alias_host,
+                             int32_t n_starts, const int32_t* start_nodes_host,
+                             const int64_t* start_prefix_host,
+                             int64_t walker_lo, int64_t walker_hi, uint64_t seed, int32_t nt,
+                             const double class_value[4],
+                             int64_t* score_host, unsigned long long* counters_host,
+                             void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NRW_H_ */

@@ -1,0 +1,390 @@
+// nrw_capi.cu -- the C ABI of libnrw.so (declared in include/nrw.h).  Plain pointers and sizes;
+// no torch types; errors are returned, never thrown.
+#include "../../../include/nrw.h"
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+#include "common.cuh"
+#include "post.cuh"
+#include "walk_philox.cuh"
+#include "walk_replay.cuh"
+
+using namespace nrw;
+
+static thread_local char g_err[512] = "";
+
+static int fail(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+#define CUDA_TRY(expr)                                                                        \
+    do {                                                                                      \
+        cudaError_t _e = (expr);                                                              \
+        if (_e != cudaSuccess)                                                                \
+            return fail(NRW_ECUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e),    \
+                        __FILE__, __LINE__);                                                  \
+    } while (0)
+
+struct nrw_engine {
+    int device;
+    int n_sms;
+    int max_smem;
+    unsigned long long* work_next;   // device counter the warps pull walker-id ranges from
+    // grow-only staging buffers of nrw_fluence_scores_host
+    void* d_rowinfo; size_t cap_rowinfo;
+    void* d_alias; size_t cap_alias;
+    void* d_starts; size_t cap_starts;
+    void* d_prefix; size_t cap_prefix;
+    void* d_score; size_t cap_score;
+    unsigned long long* d_counters;
+};
+
+extern "C" int nrw_abi_version(void) { return NRW_ABI_VERSION; }
+extern "C" const char* nrw_last_error(void) { return g_err; }
+
+extern "C" int nrw_create(int device, nrw_engine** out) {
+    if (!out) return fail(NRW_EINVAL, "nrw_create: out is NULL");
+    *out = nullptr;
+    int n = 0;
+    CUDA_TRY(cudaGetDeviceCount(&n));
+    if (device < 0 || device >= n) return fail(NRW_EINVAL, "nrw_create: device %d of %d", device, n);
+    CUDA_TRY(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10)
+        return fail(NRW_EINVAL, "nrw_create: device %d is sm_%d%d; libnrw is built for sm_100a only",
+                    device, prop.major, prop.minor);
+    nrw_engine* e = new nrw_engine();
+    memset(e, 0, sizeof(*e));
+    e->device = device;
+    e->n_sms = prop.multiProcessorCount;
+    e->max_smem = (int)prop.sharedMemPerBlockOptin;
+    CUDA_TRY(cudaMalloc(&e->work_next, sizeof(unsigned long long)));
+    CUDA_TRY(cudaMalloc(&e->d_counters, NRW_N_COUNTERS * sizeof(unsigned long long)));
+    *out = e;
+    return NRW_OK;
+}
+
+extern "C" int nrw_destroy(nrw_engine* e) {
+    if (!e) return NRW_OK;
+    cudaSetDevice(e->device);
+    cudaFree(e->work_next);
+    cudaFree(e->d_counters);
+    cudaFree(e->d_rowinfo); cudaFree(e->d_alias); cudaFree(e->d_starts);
+    cudaFree(e->d_prefix); cudaFree(e->d_score);
+    delete e;
+    return NRW_OK;
+}
+
+extern "C" int nrw_device_info(nrw_engine* e, int* n_sms, int* max_smem_bytes) {
+    if (!e) return fail(NRW_EINVAL, "nrw_device_info: engine is NULL");
+    if (n_sms) *n_sms = e->n_sms;
+    if (max_smem_bytes) *max_smem_bytes = e->max_smem;
+    return NRW_OK;
+}
+
+// ---- K4 ---------------------------------------------------------------------------------------
+extern "C" int nrw_build_cum(nrw_engine* e, int32_t n_rows, const int32_t* indptr,
+                             const double* vals, double* cum, void* stream) {
+    if (!e || !indptr || !vals || !cum || n_rows < 0) return fail(NRW_EINVAL, "nrw_build_cum: bad argument");
+    if (n_rows == 0) return NRW_OK;
+    CUDA_TRY(cudaSetDevice(e->device));
+    build_cum_kernel<<<(n_rows + 255) / 256, 256, 0, (cudaStream_t)stream>>>(n_rows, indptr, vals, cum);
+    CUDA_TRY(cudaGetLastError());
+    return NRW_OK;
+}
+
+// ---- K3 ---------------------------------------------------------------------------------------
+extern "C" int nrw_assemble_events(nrw_engine* e, int32_t n_starts, const int64_t* ev_offsets,
+                                   const int32_t* ev_t, const int32_t* ev_node,
+                                   const int64_t* ev_count, const double* time_weight,
+                                   const double* src, double v, double dt,
+                                   const int64_t* start_counts, int32_t nt, int32_t n_live,
+                                   double* out, void* stream) {
+    if (!e || !ev_offsets || !time_weight || !src || !start_counts || !out || n_starts < 0)
+        return fail(NRW_EINVAL, "nrw_assemble_events: bad argument");
+    if (n_starts == 0) return NRW_OK;
+    CUDA_TRY(cudaSetDevice(e->device));
+    assemble_events_kernel<<<(n_starts + 127) / 128, 128, 0, (cudaStream_t)stream>>>(
+        n_starts, (const long long*)ev_offsets, ev_t, ev_node, (const long long*)ev_count,
+        time_weight, src, v, dt, (const long long*)start_counts, nt, n_live, out);
+    CUDA_TRY(cudaGetLastError());
+    return NRW_OK;
+}
+
+// ---- K5 ---------------------------------------------------------------------------------------
+extern "C" int nrw_expand_events(nrw_engine* e, int64_t n_events, const int32_t* ev_t,
+                                 const int32_t* ev_node, const int64_t* ev_count, int32_t n_rows,
+                                 int32_t nt, double* out, void* stream) {
+    if (!e || !out || n_rows <= 0 || nt <= 0 || n_events < 0)
+        return fail(NRW_EINVAL, "nrw_expand_events: bad argument");
+    CUDA_TRY(cudaSetDevice(e->device));
+    CUDA_TRY(cudaMemsetAsync(out, 0, (size_t)n_rows * nt * sizeof(double), (cudaStream_t)stream));
+    if (n_events > 0) {
+        const long long blocks = (n_events + 255) / 256;
+        expand_events_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(
+            n_events, ev_t, ev_node, (const long long*)ev_count, n_rows, nt, out);
+        CUDA_TRY(cudaGetLastError());
+    }
+    return NRW_OK;
+}
+
+extern "C" int nrw_expand_counts(nrw_engine* e, const uint32_t* count_tn, int32_t t_cap,
+                                 int32_t n_rows, int32_t nt, int32_t start_node,
+                                 int64_t start_count, double* out, void* stream) {
+    if (!e || !count_tn || !out || n_rows <= 0 || nt <= 0 || t_cap <= 0)
+        return fail(NRW_EINVAL, "nrw_expand_counts: bad argument");
+    CUDA_TRY(cudaSetDevice(e->device));
+    dim3 grid((nt + 31) / 32, (n_rows + 31) / 32), block(32, 8);
+    if (grid.y > 65535) return fail(NRW_EINVAL, "nrw_expand_counts: n_rows too large for a dense tempdata");
+    expand_counts_kernel<<<grid, block, 0, (cudaStream_t)stream>>>(count_tn, t_cap, n_rows, nt,
+                                                                   start_node, start_count, out);
+    CUDA_TRY(cudaGetLastError());
+    return NRW_OK;
+}
+
+// ---- K1: plan + launch ------------------------------------------------------------------------
+struct WalkPlan {
+    int tab, tl, grid, smem;
+    WalkParams p;
+    const void* fn;
+    const char* name;
+};
+
+#define NRW_WALK_VARIANTS(X)                                                                   \
+    X(TAB_SMEM, 1) X(TAB_SMEM, 3) X(TAB_SMEM, 4) X(TAB_SMEM, 5) X(TAB_SMEM, 7) X(TAB_SMEM, 8)  \
+    X(TAB_SMEM, 9) X(TAB_SMEM, 11) X(TAB_SMEM, 16) X(TAB_SMEM, 32)                             \
+    X(TAB_HYB, 1) X(TAB_HYB, 3) X(TAB_HYB, 4) X(TAB_HYB, 5) X(TAB_HYB, 8) X(TAB_HYB, 9)        \
+    X(TAB_HYB, 32)                                                                             \
+    X(TAB_GLB, 1) X(TAB_GLB, 3) X(TAB_GLB, 8) X(TAB_GLB, 9) X(TAB_GLB, 16) X(TAB_GLB, 32)      \
+    X(TAB_CDF, 1) X(TAB_CDF, 3) X(TAB_CDF, 8) X(TAB_CDF, 9) X(TAB_CDF, 16) X(TAB_CDF, 32)
+
+static int align16(int x) { return (x + 15) & ~15; }
+
+static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, WalkPlan* plan) {
+    if (!e || !t || !w) return fail(NRW_EINVAL, "nrw_walk_philox: NULL argument");
+    if (t->n_rows <= 0 || t->n_live < 0 || t->n_live > t->n_rows)
+        return fail(NRW_EINVAL, "nrw_walk_philox: n_rows=%d n_live=%d", t->n_rows, t->n_live);
+    if (w->n_starts <= 0 || !w->start_nodes || !w->start_prefix)
+        return fail(NRW_EINVAL, "nrw_walk_philox: empty start list");
+    if (w->walker_lo < 0 || w->walker_hi < w->walker_lo || w->walker_hi >= (1ll << 40))
+        return fail(NRW_EINVAL, "nrw_walk_philox: walker id range [%lld, %lld) (ids must be < 2^40)",
+                    (long long)w->walker_lo, (long long)w->walker_hi);
+    if (w->nt < 1 || w->nt >= (1 << 24))
+        return fail(NRW_EINVAL, "nrw_walk_philox: nt=%d outside [1, 2^24)", w->nt);
+    if (!w->score && !w->node_hist && !w->count_tn)
+        return fail(NRW_EINVAL, "nrw_walk_philox: no tally requested");
+    if (w->time_weight && !w->score)
+        return fail(NRW_EINVAL, "nrw_walk_philox: time_weight without score");
+
+    WalkParams& p = plan->p;
+    memset(&p, 0, sizeof(p));
+    p.n_rows = t->n_rows; p.n_live = t->n_live; p.n_alias = t->n_alias;
+    p.indptr = t->indptr; p.cols = t->cols; p.cum = t->cum; p.node_class = t->node_class;
+    p.rowinfo = t->rowinfo; p.alias = t->alias;
+    p.n_starts = w->n_starts; p.start_nodes = w->start_nodes;
+    p.start_prefix = (const long long*)w->start_prefix;
+    p.lo = w->walker_lo; p.hi = w->walker_hi;
+    p.key = seed_to_key(w->seed); p.nt = w->nt;
+    p.score = (long long*)w->score; p.score_sq = w->score_sq; p.tw = w->time_weight;
+    for (int i = 0; i < 4; ++i) {
+        p.cv[i] = w->class_value[i];
+        p.cw[i] = (long long)w->class_value[i];
+        if (!w->time_weight && w->score && (double)p.cw[i] != w->class_value[i])
+            return fail(NRW_EINVAL, "nrw_walk_philox: class_value[%d]=%g must be an integer when "
+                        "time_weight is NULL", i, w->class_value[i]);
+    }
+    p.node_hist = w->node_hist; p.count_tn = w->count_tn;
+    p.t_cap = w->t_cap; p.per_start = w->count_per_start;
+    p.counters = w->counters; p.work_next = e->work_next;
+    if (w->count_tn && w->t_cap < 1) return fail(NRW_EINVAL, "nrw_walk_philox: t_cap=%d", w->t_cap);
+
+    // table location
+    int smem = 16, tab;
+    if (w->sampler == NRW_SAMPLER_CDF) {
+        if (!t->indptr || !t->cols || !t->cum)
+            return fail(NRW_EINVAL, "nrw_walk_philox: cdf sampler needs indptr/cols/cum");
+        tab = TAB_CDF;
+    } else if (w->sampler == NRW_SAMPLER_ALIAS) {
+        if (!t->rowinfo || !t->alias || t->n_alias <= 0)
+            return fail(NRW_EINVAL, "nrw_walk_philox: alias sampler needs rowinfo/alias tables");
+        if (t->alias_layout == NRW_ALIAS_WIDE) {
+            tab = TAB_GLB;
+        } else if (t->alias_layout == NRW_ALIAS_COMPACT) {
+            if (t->n_alias > (1 << 20))
+                return fail(NRW_EINVAL, "nrw_walk_philox: compact layout holds < 2^20 alias entries");
+            const int ab = align16(t->n_alias * 8), rb = align16(t->n_rows * 8);
+            if (16 + ab + rb <= e->max_smem) tab = TAB_SMEM;
+            else if (16 + ab <= e->max_smem) tab = TAB_HYB;
+            else return fail(NRW_ENOSPC, "nrw_walk_philox: %d compact alias entries exceed shared "
+                             "memory (%d B); use the wide layout", t->n_alias, e->max_smem);
+            p.sm_alias = smem; smem += ab;
+            if (tab == TAB_SMEM) { p.sm_rowinfo = smem; smem += rb; }
+        } else {
+            return fail(NRW_EINVAL, "nrw_walk_philox: alias_layout=%d", t->alias_layout);
+        }
+    } else {
+        return fail(NRW_EINVAL, "nrw_walk_philox: sampler=%d", w->sampler);
+    }
+
+    // tallies
+    int tl = 0;
+    if (w->score) tl |= TL_SCORE | (w->time_weight ? TL_TW : 0);
+    if (w->node_hist) {
+        const int hb = align16(t->n_rows * 4);
+        if ((tab == TAB_SMEM || tab == TAB_HYB) && smem + hb <= e->max_smem) {
+            tl |= TL_HIST_S; p.sm_hist = smem; smem += hb;
+        } else {
+            tl |= TL_HIST_G;
+        }
+    }
+    if (w->count_tn) {
+        const long long groups = w->count_per_start ? w->n_starts : 1;
+        const long long bins = groups * (long long)w->t_cap * t->n_rows;
+        if (bins <= 0 || bins >= (1ll << 40)) return fail(NRW_EINVAL, "nrw_walk_philox: %lld count bins", bins);
+        if (tab != TAB_HYB && bins * 4 + smem <= e->max_smem && bins <= 32768) {
+            tl |= TL_CNT_S; p.sm_cnt = smem; smem += align16((int)bins * 4); p.cnt_bins = (int)bins;
+        } else {
+            tl |= TL_CNT_G;
+        }
+    }
+    plan->tab = tab; plan->tl = tl; plan->smem = smem;
+
+    const long long n = w->walker_hi - w->walker_lo;
+    long long grid = (n + WALK_THREADS - 1) / WALK_THREADS;
+    if (grid < 1) grid = 1;
+    if (grid > e->n_sms) grid = e->n_sms;
+    plan->grid = (int)grid;
+    long long range = n / (grid * (WALK_THREADS / 32) * 8);
+    range = (range / 32) * 32;
+    if (range < 32) range = 32;
+    if (range > 4096) range = 4096;
+    p.range = range;
+
+    plan->fn = nullptr; plan->name = "";
+#define X(TAB, TL)                                                           \
+    if (tab == TAB && tl == TL) {                                            \
+        plan->fn = (const void*)walk_philox_kernel<TAB, TL>;                 \
+        plan->name = "walk_philox<" #TAB "," #TL ">";                        \
+    }
+    NRW_WALK_VARIANTS(X)
+#undef X
+    if (!plan->fn)
+        return fail(NRW_EINVAL, "nrw_walk_philox: tally combination %d is not built for table mode %d "
+                    "(score=1 time_weight=2 hist_smem=4 hist_global=8 count_smem=16 count_global=32)",
+                    tl, tab);
+    return NRW_OK;
+}
+
+extern "C" int nrw_walk_philox_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, char* name,
+                                    int name_len, int* grid, int* block, int* smem_bytes) {
+    WalkPlan plan;
+    const int rc = make_plan(e, t, w, &plan);
+    if (rc) return rc;
+    if (name && name_len > 0) { strncpy(name, plan.name, name_len - 1); name[name_len - 1] = 0; }
+    if (grid) *grid = plan.grid;
+    if (block) *block = WALK_THREADS;
+    if (smem_bytes) *smem_bytes = plan.smem;
+    return NRW_OK;
+}
+
+extern "C" int nrw_walk_philox(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, void* stream) {
+    WalkPlan plan;
+    const int rc = make_plan(e, t, w, &plan);
+    if (rc) return rc;
+    if (w->walker_hi == w->walker_lo) return NRW_OK;
+    CUDA_TRY(cudaSetDevice(e->device));
+    CUDA_TRY(cudaFuncSetAttribute(plan.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, plan.smem));
+    CUDA_TRY(cudaMemsetAsync(e->work_next, 0, sizeof(unsigned long long), (cudaStream_t)stream));
+    void* args[] = {&plan.p};
+    CUDA_TRY(cudaLaunchKernel(plan.fn, dim3(plan.grid), dim3(WALK_THREADS), args, plan.smem,
+                              (cudaStream_t)stream));
+    return NRW_OK;
+}
+
+// ---- K2 ---------------------------------------------------------------------------------------
+extern "C" int nrw_walk_replay(nrw_engine* e, const nrw_tables* t, const nrw_replay* r, void* stream) {
+    if (!e || !t || !r) return fail(NRW_EINVAL, "nrw_walk_replay: NULL argument");
+    if (!t->indptr || !t->cols || !t->cum) return fail(NRW_EINVAL, "nrw_walk_replay: needs indptr/cols/cum");
+    if (r->n_starts <= 0 || !r->start_nodes || !r->start_counts || r->nt < 1)
+        return fail(NRW_EINVAL, "nrw_walk_replay: bad start list / nt");
+    if (!r->u_stream || r->u_len < 0 || !r->ev_t || !r->ev_node || !r->ev_count || !r->ev_offsets ||
+        !r->scratch || !r->state)
+        return fail(NRW_EINVAL, "nrw_walk_replay: NULL buffer");
+    ReplayParams p;
+    p.n_rows = t->n_rows; p.n_live = t->n_live;
+    p.indptr = t->indptr; p.cols = t->cols; p.cum = t->cum;
+    p.n_starts = r->n_starts; p.start_nodes = r->start_nodes;
+    p.start_counts = (const long long*)r->start_counts; p.nt = r->nt;
+    p.u = r->u_stream; p.u_len = r->u_len; p.u_base = r->u_base;
+    p.ev_t = r->ev_t; p.ev_node = r->ev_node; p.ev_count = (long long*)r->ev_count;
+    p.ev_cap = r->ev_cap; p.ev_offsets = (long long*)r->ev_offsets;
+    p.scratch = r->scratch; p.state = (long long*)r->state;
+    CUDA_TRY(cudaSetDevice(e->device));
+    walk_replay_kernel<<<1, REPLAY_THREADS, 0, (cudaStream_t)stream>>>(p);
+    CUDA_TRY(cudaGetLastError());
+    return NRW_OK;
+}
+
+// ---- end-to-end with host buffers -------------------------------------------------------------
+static int grow(void** buf, size_t* cap, size_t need) {
+    if (need <= *cap) return NRW_OK;
+    if (*buf) cudaFree(*buf);
+    *buf = nullptr; *cap = 0;
+    size_t want = need + need / 4 + 256;
+    cudaError_t err = cudaMalloc(buf, want);
+    if (err != cudaSuccess) return fail(NRW_ECUDA, "cudaMalloc(%zu) failed: %s", want, cudaGetErrorString(err));
+    *cap = want;
+    return NRW_OK;
+}
+
+extern "C" int nrw_fluence_scores_host(nrw_engine* e, int32_t n_rows, int32_t n_live, int32_t n_alias,
+                                       const void* rowinfo_host, const void* alias_host,
+                                       int32_t n_starts, const int32_t* start_nodes_host,
+                                       const int64_t* start_prefix_host, int64_t walker_lo,
+                                       int64_t walker_hi, uint64_t seed, int32_t nt,
+                                       const double class_value[4], int64_t* score_host,
+                                       unsigned long long* counters_host, void* stream) {
+    if (!e || !rowinfo_host || !alias_host || !start_nodes_host || !start_prefix_host || !score_host ||
+        !class_value || n_rows <= 0 || n_alias <= 0 || n_starts <= 0)
+        return fail(NRW_EINVAL, "nrw_fluence_scores_host: bad argument");
+    cudaStream_t st = (cudaStream_t)stream;
+    CUDA_TRY(cudaSetDevice(e->device));
+    const size_t rb = (size_t)align16(n_rows * 8), ab = (size_t)align16(n_alias * 8);
+    int rc;
+    if ((rc = grow(&e->d_rowinfo, &e->cap_rowinfo, rb))) return rc;
+    if ((rc = grow(&e->d_alias, &e->cap_alias, ab))) return rc;
+    if ((rc = grow(&e->d_starts, &e->cap_starts, (size_t)n_starts * 4))) return rc;
+    if ((rc = grow(&e->d_prefix, &e->cap_prefix, (size_t)(n_starts + 1) * 8))) return rc;
+    if ((rc = grow(&e->d_score, &e->cap_score, (size_t)n_starts * 8))) return rc;
+    CUDA_TRY(cudaMemcpyAsync(e->d_rowinfo, rowinfo_host, (size_t)n_rows * 8, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(e->d_alias, alias_host, (size_t)n_alias * 8, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(e->d_starts, start_nodes_host, (size_t)n_starts * 4, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(e->d_prefix, start_prefix_host, (size_t)(n_starts + 1) * 8, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemsetAsync(e->d_score, 0, (size_t)n_starts * 8, st));
+    CUDA_TRY(cudaMemsetAsync(e->d_counters, 0, NRW_N_COUNTERS * sizeof(unsigned long long), st));
+    nrw_tables t;
+    memset(&t, 0, sizeof(t));
+    t.n_rows = n_rows; t.n_live = n_live; t.alias_layout = NRW_ALIAS_COMPACT; t.n_alias = n_alias;
+    t.rowinfo = e->d_rowinfo; t.alias = e->d_alias;
+    nrw_walk w;
+    memset(&w, 0, sizeof(w));
+    w.n_starts = n_starts; w.start_nodes = (const int32_t*)e->d_starts;
+    w.start_prefix = (const int64_t*)e->d_prefix;
+    w.walker_lo = walker_lo; w.walker_hi = walker_hi; w.seed = seed; w.nt = nt;
+    w.sampler = NRW_SAMPLER_ALIAS; w.score = (int64_t*)e->d_score;
+    for (int i = 0; i < 4; ++i) w.class_value[i] = class_value[i];
+    w.counters = e->d_counters;
+    if ((rc = nrw_walk_philox(e, &t, &w, stream))) return rc;
+    CUDA_TRY(cudaMemcpyAsync(score_host, e->d_score, (size_t)n_starts * 8, cudaMemcpyDeviceToHost, st));
+    if (counters_host)
+        CUDA_TRY(cudaMemcpyAsync(counters_host, e->d_counters, NRW_N_COUNTERS * sizeof(unsigned long long),
+                                 cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    return NRW_OK;
+}

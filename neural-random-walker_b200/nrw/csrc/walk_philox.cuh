@@ -1,0 +1,321 @@
+// walk_philox.cuh -- K1: the on-device random-walk engine (statistical mode).
+//
+// Replaces the triple loop of run_pc (fluence_mini_app.py:236-245, simple_flux_miniapp.py:189-201)
+// for ALL start nodes of run() (fluence_mini_app.py:397-407) in one launch:
+//   * one thread per walker; a lane whose walker was absorbed / left through the sink is refilled
+//     at once from the warp's walker-id cursor (warp vote: __ballot_sync + popc ranks the dead
+//     lanes; no atomics), so lanes stay busy although the mean walk is only ~2 steps long;
+//   * warps pull contiguous walker-id ranges from one global counter (dynamic balance, one
+//     atomic per `range` walkers);
+//   * Philox2x32-10 keyed by the seed with counter (walker id, step): any walker's trajectory is
+//     a pure function of (seed, id), independent of grid shape and of how ranks shard the ids;
+//   * transition tables: de-duplicated alias patterns + per-row descriptors staged ONCE per CTA
+//     into shared memory with 1-D TMA bulk copies (UBLKCP) when they fit (TAB_SMEM), descriptors
+//     left L2-resident when only the patterns fit (TAB_HYB), everything L2-resident for arbitrary
+//     graphs (TAB_GLB); TAB_CDF runs the reference's own searchsorted on the fp64 prefix sums;
+//   * tallies: per-start score in registers (fused fluence_mini_app.py:428-434), occupancy in a
+//     per-CTA shared-memory histogram merged once (sink exits aggregated by warp vote), and
+//     time-resolved counts (tempdata) in shared memory with __match_any_sync aggregation or in
+//     global memory.
+#pragma once
+#include "common.cuh"
+
+namespace nrw {
+
+enum : int { TAB_SMEM = 0, TAB_HYB = 1, TAB_GLB = 2, TAB_CDF = 3 };
+enum : int { TL_SCORE = 1, TL_TW = 2, TL_HIST_S = 4, TL_HIST_G = 8, TL_CNT_S = 16, TL_CNT_G = 32 };
+
+constexpr int WALK_THREADS = 1024;
+
+struct WalkParams {
+    int n_rows, n_live, n_alias;
+    const int32_t* indptr; const int32_t* cols; const double* cum; const uint8_t* node_class;
+    const void* rowinfo; const void* alias;
+    int n_starts; const int32_t* start_nodes; const long long* start_prefix;
+    long long lo, hi;
+    uint32_t key; int nt;
+    long long* score; double* score_sq;
+    long long cw[4]; double cv[4]; const double* tw;
+    unsigned long long* node_hist;
+    uint32_t* count_tn; int t_cap; int per_start; int cnt_bins;
+    unsigned long long* counters;
+    unsigned long long* work_next; long long range;
+    // shared-memory carve-up (byte offsets into dynamic smem)
+    int sm_rowinfo, sm_alias, sm_hist, sm_cnt;
+};
+
+template <int TAB>
+struct RowRegs { uint32_t a, b, c, d; };   // COMPACT: a=w0 b=w1 | WIDE: off,n,base,cls | CDF: a=k b=n d=cls
+
+template <int TAB>
+__device__ __forceinline__ RowRegs<TAB> load_row(const WalkParams& p, const uint2* rowinfo_s, int k) {
+    RowRegs<TAB> r;
+    if constexpr (TAB == TAB_SMEM) {
+        const uint2 v = rowinfo_s[k];
+        r.a = v.x; r.b = v.y; r.c = 0; r.d = 0;
+    } else if constexpr (TAB == TAB_HYB) {
+        const uint2 v = __ldg(reinterpret_cast<const uint2*>(p.rowinfo) + k);
+        r.a = v.x; r.b = v.y; r.c = 0; r.d = 0;
+    } else if constexpr (TAB == TAB_GLB) {
+        const uint4 v = __ldg(reinterpret_cast<const uint4*>(p.rowinfo) + k);
+        r.a = v.x; r.b = v.y; r.c = v.z; r.d = v.w;
+    } else {
+        r.a = (uint32_t)k;
+        r.b = (k < p.n_live) ? (uint32_t)(__ldg(p.indptr + k + 1) - __ldg(p.indptr + k)) : 0u;
+        r.c = 0;
+        r.d = p.node_class ? (uint32_t)__ldg(p.node_class + k) : 0u;
+    }
+    return r;
+}
+template <int TAB>
+__device__ __forceinline__ uint32_t row_n(const RowRegs<TAB>& r) {
+    if constexpr (TAB == TAB_SMEM || TAB == TAB_HYB) return (r.a >> 20) & 0x3ffu;
+    else return r.b;
+}
+template <int TAB>
+__device__ __forceinline__ uint32_t row_cls(const RowRegs<TAB>& r) {
+    if constexpr (TAB == TAB_SMEM || TAB == TAB_HYB) return r.a >> 30;
+    else return r.d & 3u;
+}
+
+template <int TAB, int TL>
+__global__ void __launch_bounds__(WALK_THREADS, 1)
+walk_philox_kernel(const __grid_constant__ WalkParams p) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    uint64_t* bar = reinterpret_cast<uint64_t*>(smem);
+    uint2* rowinfo_s = reinterpret_cast<uint2*>(smem + p.sm_rowinfo);
+    uint2* alias_s = reinterpret_cast<uint2*>(smem + p.sm_alias);
+    uint32_t* hist_s = reinterpret_cast<uint32_t*>(smem + p.sm_hist);
+    uint32_t* cnt_s = reinterpret_cast<uint32_t*>(smem + p.sm_cnt);
+    const int tid = threadIdx.x, lane = tid & 31;
+
+    // ---- stage the tables: TMA bulk copies complete on one mbarrier ---------------------------
+    constexpr bool kStage = (TAB == TAB_SMEM || TAB == TAB_HYB);
+    if constexpr (kStage) {
+        if (tid == 0) mbar_init(bar, 1);
+        __syncthreads();
+        const uint32_t alias_bytes = ((uint32_t)p.n_alias * 8u) & ~15u;
+        const uint32_t row_bytes = (TAB == TAB_SMEM) ? (((uint32_t)p.n_rows * 8u) & ~15u) : 0u;
+        if (tid == 0) {
+            mbar_expect_tx(bar, alias_bytes + row_bytes);
+            for (uint32_t o = 0; o < alias_bytes; o += 32768u)
+                tma_bulk_g2s(reinterpret_cast<unsigned char*>(alias_s) + o,
+                             reinterpret_cast<const unsigned char*>(p.alias) + o,
+                             min(32768u, alias_bytes - o), bar);
+            for (uint32_t o = 0; o < row_bytes; o += 32768u)
+                tma_bulk_g2s(reinterpret_cast<unsigned char*>(rowinfo_s) + o,
+                             reinterpret_cast<const unsigned char*>(p.rowinfo) + o,
+                             min(32768u, row_bytes - o), bar);
+        }
+        if (tid == 32) {   // an odd entry count leaves one 8-byte tail outside the 16-byte granules
+            if (p.n_alias & 1)
+                alias_s[p.n_alias - 1] = __ldg(reinterpret_cast<const uint2*>(p.alias) + p.n_alias - 1);
+            if (TAB == TAB_SMEM && (p.n_rows & 1))
+                rowinfo_s[p.n_rows - 1] = __ldg(reinterpret_cast<const uint2*>(p.rowinfo) + p.n_rows - 1);
+        }
+    }
+    if constexpr (TL & TL_HIST_S)
+        for (int i = tid; i < p.n_rows; i += WALK_THREADS) hist_s[i] = 0u;
+    if constexpr (TL & TL_CNT_S)
+        for (int i = tid; i < p.cnt_bins; i += WALK_THREADS) cnt_s[i] = 0u;
+    if constexpr (kStage) mbar_wait(bar, 0);
+    __syncthreads();
+
+    const uint32_t key = p.key;
+    const int t_last = p.nt - 1;        // last model step (fluence_mini_app.py:236)
+    const int t_score_max = p.nt - 2;   // solution sum skips the final step (:428, Q3)
+
+    // ---- lane state ------------------------------------------------------------------------------
+    bool alive = false;
+    uint32_t c0 = 0, chi = 0;           // Philox counter: walker id (low 32 | bits 32..39 << 24)
+    int t = 0;
+    RowRegs<TAB> row{0, 0, 0, 0};
+    long long x = 0;                    // this walker's score
+    int s = -1;                         // start index the lane is accumulating for
+    long long s_lo = 0, s_end = 0;
+    RowRegs<TAB> srow{0, 0, 0, 0};
+    long long acc = 0; double acc2 = 0.0;
+    unsigned long long nsteps = 0;
+    uint32_t nexit = 0, nsurv = 0, nwalk = 0, novf = 0, sinkc = 0;
+    // warp-uniform
+    long long cursor = 0, range_end = 0;
+    bool exhausted = false;
+
+    auto flush_score = [&]() {
+        if constexpr (TL & TL_SCORE) {
+            if (s >= 0) {
+                if (acc != 0) atomicAdd(reinterpret_cast<unsigned long long*>(p.score) + s,
+                                        (unsigned long long)acc);
+                if (p.score_sq && acc2 != 0.0) atomicAdd(p.score_sq + s, acc2);
+            }
+            acc = 0; acc2 = 0.0;
+        }
+    };
+
+    while (true) {
+        // ---- refill dead lanes (warp vote ranks them) ---------------------------------------
+        const unsigned need = __ballot_sync(NRW_FULL_MASK, !alive);
+        if (need) {
+            if (cursor >= range_end && !exhausted) {
+                long long a = 0;
+                if (lane == 0) a = (long long)atomicAdd(p.work_next, (unsigned long long)p.range);
+                a = __shfl_sync(NRW_FULL_MASK, a, 0);
+                cursor = p.lo + a;
+                if (cursor >= p.hi) { exhausted = true; cursor = range_end = p.hi; }
+                else range_end = min(cursor + p.range, p.hi);
+            }
+            const int rank = __popc(need & lanemask_lt());
+            const long long gnew = cursor + rank;
+            const bool take = !alive && gnew < range_end;
+            cursor = min(cursor + (long long)__popc(need), range_end);
+            if (take) {
+                if (gnew >= s_end || gnew < s_lo) {
+                    flush_score();
+                    bool found = false;
+                    if (s >= 0 && gnew >= s_end && s + 1 < p.n_starts) {
+                        const long long e2 = __ldg(p.start_prefix + s + 2);
+                        if (gnew < e2) { ++s; s_lo = s_end; s_end = e2; found = true; }
+                    }
+                    if (!found) {
+                        int lo_i = 0, hi_i = p.n_starts;
+                        while (hi_i - lo_i > 1) {
+                            const int mid = (lo_i + hi_i) >> 1;
+                            if (__ldg(p.start_prefix + mid) <= gnew) lo_i = mid; else hi_i = mid;
+                        }
+                        s = lo_i;
+                        s_lo = __ldg(p.start_prefix + s);
+                        s_end = __ldg(p.start_prefix + s + 1);
+                    }
+                    srow = load_row<TAB>(p, rowinfo_s, __ldg(p.start_nodes + s));
+                }
+                row = srow;
+                c0 = (uint32_t)gnew;
+                chi = (uint32_t)((unsigned long long)gnew >> 32) << 24;
+                t = 0; x = 0;
+                ++nwalk;
+                alive = (row_n<TAB>(row) > 0u) && (t_last >= 1);
+                if (!alive) { if (row_n<TAB>(row) == 0u) ++nexit; else ++nsurv; }
+            }
+        }
+        if (!__any_sync(NRW_FULL_MASK, alive)) {
+            if (exhausted) break;
+            continue;
+        }
+
+        // ---- one model step for every live lane ---------------------------------------------
+        const bool stepped = alive;
+        int knew = 0;
+        if (stepped) {
+            ++t; ++nsteps;
+            const uint2 r = philox2x32_10(c0, chi | (uint32_t)t, key);
+            if constexpr (TAB == TAB_CDF) {
+                knew = sample_cdf(p.indptr, p.cols, p.cum, (int)row.a, u53(r.x, r.y));
+            } else if constexpr (TAB == TAB_GLB) {
+                const uint32_t slot = __umulhi(r.x, row.b);
+                const uint4 e = __ldg(reinterpret_cast<const uint4*>(p.alias) + row.a + slot);
+                knew = (int)(row.c + ((r.y <= e.x) ? e.y : e.z));
+            } else {
+                const uint32_t n = (row.a >> 20) & 0x3ffu, off = row.a & 0xfffffu;
+                const uint32_t slot = __umulhi(r.x, n);
+                const uint2 e = alias_s[off + slot];
+                knew = (int)(row.b + ((r.y <= e.x) ? (e.y & 0xffffu) : (e.y >> 16)));
+            }
+            row = load_row<TAB>(p, rowinfo_s, knew);
+        }
+        const bool in_sum = stepped && (t <= t_score_max);
+
+        // ---- tallies --------------------------------------------------------------------------------
+        if constexpr (TL & TL_SCORE) {
+            if (in_sum) {
+                const uint32_t cls = row_cls<TAB>(row);
+                if constexpr (TL & TL_TW) {
+                    const double cvv = cls == 0 ? p.cv[0] : cls == 1 ? p.cv[1] : cls == 2 ? p.cv[2] : p.cv[3];
+                    x += __double2ll_rn(__ldg(p.tw + t) * cvv);
+                } else {
+                    x += cls == 0 ? p.cw[0] : cls == 1 ? p.cw[1] : cls == 2 ? p.cw[2] : p.cw[3];
+                }
+            }
+        }
+        if constexpr (TL & (TL_HIST_S | TL_HIST_G)) {
+            // sink exits are the one hot bin: aggregate them with a warp vote
+            const bool hot = in_sum && (knew == p.n_rows - 1);
+            const unsigned hm = __ballot_sync(NRW_FULL_MASK, hot);
+            if (lane == 0) sinkc += __popc(hm);
+            if (in_sum && !hot) {
+                if constexpr (TL & TL_HIST_S) atomicAdd(hist_s + knew, 1u);
+                else atomicAdd(p.node_hist + knew, 1ull);
+            }
+        }
+        if constexpr (TL & TL_CNT_S) {
+            const int gq = p.per_start ? s : 0;
+            int bin = -1;
+            if (stepped) {
+                if (t < p.t_cap) bin = (gq * p.t_cap + t) * p.n_rows + knew; else ++novf;
+            }
+            const unsigned m = __match_any_sync(NRW_FULL_MASK, bin);
+            if (bin >= 0 && lane == __ffs(m) - 1) atomicAdd(cnt_s + bin, (uint32_t)__popc(m));
+        }
+        if constexpr (TL & TL_CNT_G) {
+            if (stepped) {
+                const long long gq = p.per_start ? s : 0;
+                if (t < p.t_cap)
+                    atomicAdd(p.count_tn + ((size_t)(gq * p.t_cap + t) * (size_t)p.n_rows + (size_t)knew), 1u);
+                else ++novf;
+            }
+        }
+
+        // ---- absorption / sink exit / end of time ------------------------------------------------
+        if (stepped) {
+            const bool absorbed = row_n<TAB>(row) == 0u;
+            if (absorbed || t >= t_last) {
+                alive = false;
+                if (absorbed) ++nexit; else ++nsurv;
+                if constexpr (TL & TL_SCORE) {
+                    acc += x;
+                    if (p.score_sq) { const double xd = (double)x; acc2 += xd * xd; }
+                }
+            }
+        }
+    }
+
+    // ---- epilogue: flush register tallies, merge the CTA histogram once ----------------------
+    flush_score();
+    if constexpr (TL & (TL_HIST_S | TL_HIST_G)) {
+        if (lane == 0 && sinkc) {
+            if constexpr (TL & TL_HIST_S) atomicAdd(hist_s + p.n_rows - 1, sinkc);
+            else atomicAdd(p.node_hist + p.n_rows - 1, (unsigned long long)sinkc);
+        }
+    }
+    unsigned long long v0 = nsteps;
+    uint32_t v1 = nexit, v2 = nsurv, v3 = novf, v4 = nwalk;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        v0 += __shfl_xor_sync(NRW_FULL_MASK, v0, o);
+        v1 += __shfl_xor_sync(NRW_FULL_MASK, v1, o);
+        v2 += __shfl_xor_sync(NRW_FULL_MASK, v2, o);
+        v3 += __shfl_xor_sync(NRW_FULL_MASK, v3, o);
+        v4 += __shfl_xor_sync(NRW_FULL_MASK, v4, o);
+    }
+    if (lane == 0 && p.counters) {
+        if (v0) atomicAdd(p.counters + 0, v0);
+        if (v1) atomicAdd(p.counters + 1, (unsigned long long)v1);
+        if (v2) atomicAdd(p.counters + 2, (unsigned long long)v2);
+        if (v3) atomicAdd(p.counters + 3, (unsigned long long)v3);
+        if (v4) atomicAdd(p.counters + 4, (unsigned long long)v4);
+    }
+    if constexpr (TL & (TL_HIST_S | TL_CNT_S)) {
+        __syncthreads();
+        if constexpr (TL & TL_HIST_S)
+            for (int i = tid; i < p.n_rows; i += WALK_THREADS) {
+                const uint32_t h = hist_s[i];
+                if (h) atomicAdd(p.node_hist + i, (unsigned long long)h);
+            }
+        if constexpr (TL & TL_CNT_S)
+            for (int i = tid; i < p.cnt_bins; i += WALK_THREADS) {
+                const uint32_t h = cnt_s[i];
+                if (h) atomicAdd(p.count_tn + i, h);
+            }
+    }
+}
+
+}  // namespace nrw
