@@ -28,6 +28,12 @@ extern "C" {
 
 #define NRW_ABI_VERSION 1
 
+#if defined(__GNUC__)
+#define NRW_API __attribute__((visibility("default")))
+#else
+#define NRW_API
+#endif
+
 #define NRW_OK            0
 #define NRW_EINVAL       -1   /* bad argument / unsupported combination            */
 #define NRW_ECUDA        -2   /* a CUDA runtime call failed (see nrw_last_error)    */
@@ -86,7 +92,11 @@ typedef struct nrw_walk {
     const int32_t* start_nodes;     /* [n_starts]                                        */
     const int64_t* start_prefix;    /* [n_starts + 1]                                    */
     int64_t  walker_lo, walker_hi;
-    uint64_t seed;                  /* Philox key; counter = (g, step block)             */
+    /* Philox stream id of walker g: start_id_base[s] + (g - start_prefix[s]), or g itself
+     * when start_id_base is NULL.  Lets a rank walk a slice of EVERY start's walkers while
+     * each walker keeps the stream it has in the unsharded run.  ids must be < 2^40.    */
+    const int64_t* start_id_base;   /* [n_starts] or NULL                                */
+    uint64_t seed;                  /* Philox key = hash(seed); counter = (stream id, step) */
     int32_t  nt;                    /* neuraltime: model steps t = 1 .. nt-1 (:236)      */
     int32_t  sampler;               /* NRW_SAMPLER_*                                     */
 
@@ -136,34 +146,34 @@ typedef struct nrw_replay {
 } nrw_replay;
 
 /* ---- API ------------------------------------------------------------------------------ */
-int  nrw_abi_version(void);
-const char* nrw_last_error(void);
+NRW_API int  nrw_abi_version(void);
+NRW_API const char* nrw_last_error(void);
 
-int  nrw_create(int device, nrw_engine** out);
-int  nrw_destroy(nrw_engine* e);
+NRW_API int  nrw_create(int device, nrw_engine** out);
+NRW_API int  nrw_destroy(nrw_engine* e);
 /* number of SMs, max opt-in shared memory per block, of the engine's device */
-int  nrw_device_info(nrw_engine* e, int* n_sms, int* max_smem_bytes);
+NRW_API int  nrw_device_info(nrw_engine* e, int* n_sms, int* max_smem_bytes);
 
 /* K4: per-row sequential fp64 prefix sums of CSR values
  * (replaces np.cumsum(myQ, axis=1), fluence_mini_app.py:224).                             */
-int  nrw_build_cum(nrw_engine* e, int32_t n_rows, const int32_t* indptr,
+NRW_API int  nrw_build_cum(nrw_engine* e, int32_t n_rows, const int32_t* indptr,
                    const double* vals, double* cum, void* stream);
 
 /* K1: replaces the loops of run_pc, fluence_mini_app.py:236-245 and
  * simple_flux_miniapp.py:189-201, for all start nodes of run() at once (:397-407).        */
-int  nrw_walk_philox(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, void* stream);
+NRW_API int  nrw_walk_philox(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, void* stream);
 /* which kernel variant nrw_walk_philox would launch: writes a short name and the launch
  * geometry (for bench / profiles); no launch.                                             */
-int  nrw_walk_philox_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w,
+NRW_API int  nrw_walk_philox_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w,
                           char* name, int name_len, int* grid, int* block, int* smem_bytes);
 
 /* K2: same loops, consuming the reference's own uniform stream in the reference's order
  * (t, node ascending, slot) -- fluence_mini_app.py:236-243, Q5/Q6 of SURVEY.md.           */
-int  nrw_walk_replay(nrw_engine* e, const nrw_tables* t, const nrw_replay* r, void* stream);
+NRW_API int  nrw_walk_replay(nrw_engine* e, const nrw_tables* t, const nrw_replay* r, void* stream);
 
 /* K3: fluence_mini_app.py:422-438 in the reference's (t, k) order, one start per thread:
  * out[s] = (sum over events of (((count*tw[t])*v)*src[k])*dt) / M[s], 1 <= t <= nt-2, k < n_live. */
-int  nrw_assemble_events(nrw_engine* e, int32_t n_starts, const int64_t* ev_offsets,
+NRW_API int  nrw_assemble_events(nrw_engine* e, int32_t n_starts, const int64_t* ev_offsets,
                          const int32_t* ev_t, const int32_t* ev_node, const int64_t* ev_count,
                          const double* time_weight, const double* src, double v, double dt,
                          const int64_t* start_counts, int32_t nt, int32_t n_live,
@@ -171,17 +181,17 @@ int  nrw_assemble_events(nrw_engine* e, int32_t n_starts, const int64_t* ev_offs
 
 /* K5: sparse events / dense uint32 counts -> the dense float64 [n_rows, nt] array that
  * run_pc returns (fluence_mini_app.py:227,247).  `out` is fully written.                  */
-int  nrw_expand_events(nrw_engine* e, int64_t n_events, const int32_t* ev_t,
+NRW_API int  nrw_expand_events(nrw_engine* e, int64_t n_events, const int32_t* ev_t,
                        const int32_t* ev_node, const int64_t* ev_count,
                        int32_t n_rows, int32_t nt, double* out, void* stream);
-int  nrw_expand_counts(nrw_engine* e, const uint32_t* count_tn, int32_t t_cap, int32_t n_rows,
+NRW_API int  nrw_expand_counts(nrw_engine* e, const uint32_t* count_tn, int32_t t_cap, int32_t n_rows,
                        int32_t nt, int32_t start_node, int64_t start_count,
                        double* out, void* stream);
 
 /* End-to-end convenience with HOST buffers (what `bench.py` times as e2e): copies the
  * compact alias tables and the start list to the device, runs K1 in score mode, copies
  * score / counters back and synchronises `stream`.                                        */
-int  nrw_fluence_scores_host(nrw_engine* e,
+NRW_API int  nrw_fluence_scores_host(nrw_engine* e,
                              int32_t n_rows, int32_t n_live, int32_t n_alias,
                              const void* rowinfo_host, const void* alias_host,
                              int32_t n_starts, const int32_t* start_nodes_host,

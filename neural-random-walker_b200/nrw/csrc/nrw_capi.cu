@@ -189,6 +189,7 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
     p.rowinfo = t->rowinfo; p.alias = t->alias;
     p.n_starts = w->n_starts; p.start_nodes = w->start_nodes;
     p.start_prefix = (const long long*)w->start_prefix;
+    p.start_id_base = (const long long*)w->start_id_base;
     p.lo = w->walker_lo; p.hi = w->walker_hi;
     p.key = seed_to_key(w->seed); p.nt = w->nt;
     p.score = (long long*)w->score; p.score_sq = w->score_sq; p.tw = w->time_weight;

@@ -31,7 +31,7 @@ struct WalkParams {
     int n_rows, n_live, n_alias;
     const int32_t* indptr; const int32_t* cols; const double* cum; const uint8_t* node_class;
     const void* rowinfo; const void* alias;
-    int n_starts; const int32_t* start_nodes; const long long* start_prefix;
+    int n_starts; const int32_t* start_nodes; const long long* start_prefix; const long long* start_id_base;
     long long lo, hi;
     uint32_t key; int nt;
     long long* score; double* score_sq;
@@ -102,10 +102,11 @@ walk_philox_kernel(const __grid_constant__ WalkParams p) {
                 tma_bulk_g2s(reinterpret_cast<unsigned char*>(alias_s) + o,
                              reinterpret_cast<const unsigned char*>(p.alias) + o,
                              min(32768u, alias_bytes - o), bar);
-            for (uint32_t o = 0; o < row_bytes; o += 32768u)
-                tma_bulk_g2s(reinterpret_cast<unsigned char*>(rowinfo_s) + o,
-                             reinterpret_cast<const unsigned char*>(p.rowinfo) + o,
-                             min(32768u, row_bytes - o), bar);
+            if constexpr (TAB == TAB_SMEM)
+                for (uint32_t o = 0; o < row_bytes; o += 32768u)
+                    tma_bulk_g2s(reinterpret_cast<unsigned char*>(rowinfo_s) + o,
+                                 reinterpret_cast<const unsigned char*>(p.rowinfo) + o,
+                                 min(32768u, row_bytes - o), bar);
         }
         if (tid == 32) {   // an odd entry count leaves one 8-byte tail outside the 16-byte granules
             if (p.n_alias & 1)
@@ -132,7 +133,7 @@ walk_philox_kernel(const __grid_constant__ WalkParams p) {
     RowRegs<TAB> row{0, 0, 0, 0};
     long long x = 0;                    // this walker's score
     int s = -1;                         // start index the lane is accumulating for
-    long long s_lo = 0, s_end = 0;
+    long long s_lo = 0, s_end = 0, s_idoff = 0;   // stream id = g + s_idoff
     RowRegs<TAB> srow{0, 0, 0, 0};
     long long acc = 0; double acc2 = 0.0;
     unsigned long long nsteps = 0;
@@ -187,10 +188,12 @@ walk_philox_kernel(const __grid_constant__ WalkParams p) {
                         s_end = __ldg(p.start_prefix + s + 1);
                     }
                     srow = load_row<TAB>(p, rowinfo_s, __ldg(p.start_nodes + s));
+                    s_idoff = p.start_id_base ? (__ldg(p.start_id_base + s) - s_lo) : 0ll;
                 }
                 row = srow;
-                c0 = (uint32_t)gnew;
-                chi = (uint32_t)((unsigned long long)gnew >> 32) << 24;
+                const unsigned long long sid = (unsigned long long)(gnew + s_idoff);
+                c0 = (uint32_t)sid;
+                chi = (uint32_t)(sid >> 32) << 24;
                 t = 0; x = 0;
                 ++nwalk;
                 alive = (row_n<TAB>(row) > 0u) && (t_last >= 1);

@@ -1,0 +1,118 @@
+"""Shared machinery behind the drop-in entry points (fluence_mini_app.run_pc / run,
+simple_flux_miniapp.run_pc / run, loihirw.rw_model.rad_test, densityrw.*).
+
+The reference's back ends share one signature (fluence_mini_app.py:218-222, :399-407):
+    run_X(matrix_filename, neuraltime, initial_walkers=[[node, M]], meshSize, runtime_args) -> float64[rows, nt]
+and the matrix travels BY FILENAME.  Here the file is parsed once and its device tables are cached,
+and two RNG modes are offered:
+  * "replay" -- consume the global legacy ``np.random`` stream exactly like the reference
+    (bit-identical tempdata / rwSol, stream left at the reference's position);
+  * "philox" -- counter-based on-device RNG (statistically equivalent, orders of magnitude faster).
+"""
+from __future__ import annotations
+
+import logging
+import os
+
+import numpy as np
+
+from . import mesh as _mesh
+from .engine import get_engine
+
+rw_logger = logging.getLogger("NRW")
+
+RNG_MODES = ("auto", "replay", "philox")
+AUTO_REPLAY_MAX_WALKERS = 1 << 22     # "auto": bit-exact replay up to ~4M walkers, Philox beyond
+SAMPLERS = ("alias", "cdf")
+
+_table_cache: dict = {}
+
+
+def resolve_rng(mode, total_walkers: int) -> str:
+    mode = mode or os.environ.get("NRW_RNG", "auto")
+    if mode not in RNG_MODES:
+        raise ValueError("rng must be one of %s" % (RNG_MODES,))
+    if mode == "auto":
+        return "replay" if total_walkers <= AUTO_REPLAY_MAX_WALKERS else "philox"
+    return mode
+
+
+def device_tables(csr, node_class=None, key=None):
+    """Upload (once) and cache the device tables of a matrix."""
+    eng = get_engine()
+    k = (id(csr) if key is None else key, None if node_class is None else node_class.tobytes(),
+         eng.device.index)
+    hit = _table_cache.get(k)
+    if hit is None:
+        if len(_table_cache) > 8:
+            _table_cache.clear()
+        hit = (eng.upload(csr, node_class=node_class), csr)      # keep csr alive: id() stays unique
+        _table_cache[k] = hit
+    return eng, hit[0]
+
+
+def philox_seed_from_global_stream() -> int:
+    """One 63-bit seed per call, drawn from the legacy global stream so that ``np.random.seed(s)``
+    (fluence_mini_app.py:523) still makes Philox-mode runs reproducible."""
+    return int(np.random.randint(0, 2 ** 63 - 1, dtype=np.int64))
+
+
+def pc_tempdata(csr, neuraltime, initial_walkers, n_out_rows, rng=None, sampler="alias"):
+    """The body of a drop-in ``run_pc``: float64 [n_out_rows, neuraltime] occupancy counts for
+    ``initial_walkers[0]`` (only element 0 is honoured, fluence_mini_app.py:229-230, Q11)."""
+    place = int(initial_walkers[0][0])
+    amount = int(initial_walkers[0][1])
+    nt = int(neuraltime)
+    if not (0 <= place < csr.n_rows):
+        raise IndexError("index %d is out of bounds for axis 0 with size %d" % (place, csr.n_rows))
+    eng, tabs = device_tables(csr)
+    mode = resolve_rng(rng, amount)
+    if amount <= 0 or nt <= 1:
+        out = np.zeros((n_out_rows, nt))
+        if nt >= 1:
+            out[place, 0] = amount
+        return out
+    if mode == "replay":
+        rep = eng.replay(tabs, [place], [amount], nt)
+        dense = eng.expand_events(rep, 0, csr.n_rows, nt)
+    else:
+        seed = philox_seed_from_global_stream()
+        t_cap = min(nt, 1024)
+        while True:
+            res = eng.walk(tabs, [place], [amount], nt, seed, sampler=sampler, count_tn=True,
+                           t_cap=t_cap)
+            if res.counters_dict()["t_overflow"] == 0 or t_cap >= nt:
+                break
+            t_cap = min(nt, t_cap * 8)       # same seed -> same trajectories, longer tally window
+        dense = eng.expand_counts(res.count_tn, res.t_cap, csr.n_rows, nt, place, amount)
+    return dense[:n_out_rows].cpu().numpy()
+
+
+def unavailable_backend(name: str, needs: str):
+    """Dispatch-table entry for the neuromorphic back ends this build does not carry."""
+    def _run(matrix_filename=None, neuraltime=None, initial_walkers=None, meshSize=None,
+             runtime_args={}):
+        raise NotImplementedError(
+            "run_mode '%s' needs %s, which this B200 build does not include; "
+            "use -r pc (same call signature and return value)" % (name, needs))
+    _run.__name__ = "run_" + name
+    return _run
+
+
+def exp_time_weights(SigA, dt, nt):
+    """w[j] = np.exp(-SigA*dt*j) evaluated scalar by scalar as fluence_mini_app.py:434 does (a
+    vectorised np.exp may take a SIMD path with different last bits)."""
+    w = np.empty(nt)
+    lim = min(nt, 1 << 16)
+    for j in range(lim):
+        w[j] = np.exp(-SigA * dt * j)
+    if lim < nt:
+        w[lim:] = np.exp(-SigA * dt * np.arange(lim, nt))
+    return w
+
+
+def time_seed():
+    """fluence_mini_app.py:519 (Q10; the '+hour*24' is the reference's, kept verbatim)."""
+    from datetime import datetime
+    return (datetime.now().microsecond + datetime.now().second + datetime.now().minute * 60
+            + datetime.now().hour * 24)

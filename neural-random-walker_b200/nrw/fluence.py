@@ -1,0 +1,104 @@
+"""Fused fluence solve: all start nodes of run() (fluence_mini_app.py:397-438) in one pass.
+
+The reference calls its back end once per start node, materialises tempdata[(meshSize+1), nt] and
+then loops over all nt*meshSize cells to form one number.  Here
+  * replay mode walks all start nodes in order on the reference's uniform stream (K2) and K3 sums
+    the sparse events in the reference's own (t, k) fp64 order -> rwSol bit-identical;
+  * philox mode runs K1 once with the per-start score tally; the dense tempdata never exists.
+"""
+from __future__ import annotations
+
+import logging
+from dataclasses import dataclass, field
+
+import numpy as np
+
+from . import dist as _dist
+from . import mesh as _mesh
+from . import tables as _tables
+from .dropin import device_tables, exp_time_weights, resolve_rng
+from .engine import get_engine
+
+rw_logger = logging.getLogger("NRW")
+
+FIXED_POINT = 4294967296.0     # 2^32: score unit of the time-weighted / multi-class tally
+
+
+@dataclass
+class FluenceResult:
+    rwSol: np.ndarray                      # [(NS-1), (ND-1)] in the reference's index layout (Q2)
+    per_start: np.ndarray                  # [meshSize] value for start node i (before the Q2 mapping)
+    walker_steps: int                      # uniform draws == walker-steps (the throughput unit)
+    rng: str
+    stderr: np.ndarray | None = None       # [meshSize] standard error of per_start (philox mode)
+    counters: dict = field(default_factory=dict)
+    kernel: str = ""
+
+
+def scatter_to_rwsol(per_start: np.ndarray, NS: int, ND: int) -> np.ndarray:
+    """Write per-start values into rwSol with the reference's index map (fluence_mini_app.py:415-419,
+    :438) in start order: rwSol[0, ND-2] is written twice (i = 0, then i = ND-1 wins) and
+    rwSol[NS-2, ND-2] is never written."""
+    nd1 = ND - 1
+    i = np.arange(len(per_start))
+    aind = i % nd1
+    aind = np.where(aind == 0, nd1, aind) - 1
+    posind = ((i - aind) / nd1).astype(np.int64)          # int() truncates toward zero
+    rwSol = np.zeros((NS - 1, nd1))
+    rwSol[posind, aind] = per_start                       # later i overwrite earlier: numpy keeps the last
+    return rwSol
+
+
+def solve_fluence(csr: _mesh.TransitionCSR, M: int, nt: int, SigA, dt, v, source=_mesh.source_default,
+                  rng=None, sampler="alias", seed=None, want_stderr=False) -> FluenceResult:
+    """rwSol for every start node of a fluence mesh built by ``mesh.build_fluence_csr``."""
+    m = csr.meta["mesh"]
+    meshSize, NS, ND = m["meshSize"], m["NS"], m["ND"]
+    srcvals = _mesh.source_values(m["meshpoints"], source)
+    mode = resolve_rng(rng, meshSize * int(M))
+    rank, world = _dist.world()
+    starts = np.arange(meshSize)
+    if mode == "replay":
+        if world > 1 and rank != 0:
+            rw_logger.info("replay mode is sequential (one shared stream): rank %d idles", rank)
+        eng, tabs = device_tables(csr)
+        rep = eng.replay(tabs, starts, M, nt)
+        tw = exp_time_weights(SigA, dt, nt)
+        out = eng.assemble_events(rep, tw, srcvals, v, dt, M, nt, meshSize)
+        per_start = out.cpu().numpy()
+        return FluenceResult(scatter_to_rwsol(per_start, NS, ND), per_start, rep.draws_used, "replay")
+
+    # ---- philox: one K1 launch, per-start score in registers -------------------------------
+    node_class, class_value = _tables.classify_source(srcvals, csr.n_rows)
+    eng, tabs = device_tables(csr, node_class=node_class)
+    if seed is None:
+        from .dropin import philox_seed_from_global_stream
+        seed = philox_seed_from_global_stream()
+    n_classes = int((class_value != 0).sum())
+    uniform_time = (float(SigA) == 0.0) and n_classes <= 1
+    if uniform_time:
+        cv = (class_value != 0).astype(np.float64)        # count hits; scale by S0 afterwards
+        unit = float(class_value[class_value != 0][0]) if n_classes else 0.0
+        tw = None
+    else:
+        cv = class_value * FIXED_POINT
+        unit = 1.0 / FIXED_POINT
+        tw = exp_time_weights(SigA, dt, nt)
+    # every rank walks the same slice of EVERY start's walkers (balanced: starts differ in lifetime)
+    lo_m, hi_m = _dist.shard_range(int(M), rank, world)
+    counts = np.full(meshSize, hi_m - lo_m, dtype=np.int64)
+    id_base = starts.astype(np.int64) * int(M) + lo_m
+    res = eng.walk(tabs, starts, counts, nt, seed, sampler=sampler, score=True,
+                   score_sq=want_stderr, class_value=cv, time_weight=tw, start_id_base=id_base)
+    _dist.allreduce_sum_([res.score, res.score_sq, res.counters])
+    score = res.score.cpu().numpy().astype(np.float64)
+    scale = unit * v * dt
+    per_start = score * scale / M
+    stderr = None
+    if want_stderr:
+        sq = res.score_sq.cpu().numpy()
+        var = np.maximum(sq / M - (score / M) ** 2, 0.0) * scale * scale
+        stderr = np.sqrt(var / M)
+    c = res.counters_dict()
+    return FluenceResult(scatter_to_rwsol(per_start, NS, ND), per_start, c["steps"], "philox",
+                         stderr=stderr, counters=c, kernel=res.kernel)

@@ -1,0 +1,214 @@
+"""Per-row sampling tables for the device: cumulative (cdf) and alias, with row-pattern dedup.
+
+The reference samples a transition with ``np.searchsorted(np.cumsum(myQ,axis=1)[j,:], u)``
+(fluence_mini_app.py:224,244).  The device keeps two equivalent forms of each row:
+
+* ``cum``   -- the sequential fp64 prefix sums over the row's non-zeros (bit-equal to the dense
+  ``np.cumsum`` at the non-zero columns).  Used by the replay kernel and the ``cdf`` sampler.
+* alias tables (Walker/Vose) -- O(1) draws for the Philox walk.  Rows of the fluence matrix are
+  translates of a few patterns (same relative columns, same probabilities), so patterns are
+  de-duplicated and each row keeps only ``(pattern offset, length, column base, source class)``:
+  the 10 001-node mesh needs 80 KB of patterns + 80 KB of row descriptors, which is what lets the
+  kernel stage everything in one SM's shared memory.
+
+Quantisation: the alias coin is a 32-bit threshold (probabilities resolved to 2^-32) and the slot
+is ``mulhi(r0, n)`` (slot probabilities equal to within n/2^32) -- both orders of magnitude below
+the Monte-Carlo error of any feasible run and stated in DESIGN.md.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+
+import numpy as np
+
+from .mesh import TransitionCSR
+
+COMPACT_MAX_N = 1023
+COMPACT_MAX_REL = 65535
+COMPACT_MAX_ENTRIES = 1 << 20
+
+
+def row_cum(csr: TransitionCSR) -> np.ndarray:
+    """Sequential fp64 prefix sums per row (host form of kernel K4 / fluence_mini_app.py:224)."""
+    cum = np.empty_like(csr.vals)
+    lens = csr.row_lengths()
+    for ln in np.unique(lens):
+        if ln == 0:
+            continue
+        rows = np.nonzero(lens == ln)[0]
+        at = csr.indptr[rows][:, None] + np.arange(ln)[None, :]
+        cum[at] = np.cumsum(csr.vals[at], axis=1)
+    return cum
+
+
+def _vose(p: np.ndarray):
+    """Walker/Vose alias table of a probability vector (normalised here).  Returns
+    (prob[n] in [0,1], alias[n])."""
+    n = len(p)
+    q = p / p.sum() * n
+    prob = np.ones(n)
+    alias = np.arange(n)
+    small = [i for i in range(n) if q[i] < 1.0]
+    large = [i for i in range(n) if q[i] >= 1.0]
+    q = q.copy()
+    while small and large:
+        s = small.pop()
+        g = large.pop()
+        prob[s] = q[s]
+        alias[s] = g
+        q[g] = (q[g] + q[s]) - 1.0
+        (small if q[g] < 1.0 else large).append(g)
+    for i in small + large:            # numerical leftovers: probability 1
+        prob[i] = 1.0
+        alias[i] = i
+    return prob, alias
+
+
+@dataclass
+class AliasTables:
+    layout: str                 # "compact" | "wide"
+    rowinfo: np.ndarray         # uint32 [n_rows, 2] (compact) / [n_rows, 4] (wide)
+    alias: np.ndarray           # uint32 [n_alias, 2] (compact) / [n_alias, 4] (wide)
+    n_patterns: int
+    pattern_of_row: np.ndarray  # int64 [n_rows], -1 for empty rows
+
+    @property
+    def n_alias(self) -> int:
+        return int(self.alias.shape[0])
+
+
+def dedup_rows(csr: TransitionCSR):
+    """Group rows whose (relative columns, values) coincide.  Returns (pattern_of_row,
+    representative_row_of_pattern, base_col_of_row)."""
+    lens = csr.row_lengths()
+    n = csr.n_rows
+    pat = np.full(n, -1, dtype=np.int64)
+    base = np.zeros(n, dtype=np.int64)
+    reps = []
+    for ln in np.unique(lens):
+        if ln == 0:
+            continue
+        rows = np.nonzero(lens == ln)[0]
+        at = csr.indptr[rows][:, None] + np.arange(ln)[None, :]
+        c = csr.cols[at].astype(np.int64)
+        b = c[:, 0]
+        rel = c - b[:, None]
+        base[rows] = b
+        key = np.concatenate([rel.astype(np.uint64), csr.vals[at].view(np.uint64)], axis=1)
+        _, first, inv = np.unique(key, axis=0, return_index=True, return_inverse=True)
+        pat[rows] = len(reps) + inv.reshape(-1)
+        reps.extend(rows[first].tolist())
+    return pat, np.array(reps, dtype=np.int64), base
+
+
+def build_alias(csr: TransitionCSR, node_class: np.ndarray | None = None,
+                layout: str = "auto") -> AliasTables:
+    """Alias tables + row descriptors in the device layouts of include/nrw.h."""
+    n = csr.n_rows
+    lens = csr.row_lengths()
+    if node_class is None:
+        node_class = np.zeros(n, dtype=np.uint8)
+    node_class = np.asarray(node_class).astype(np.uint32)
+    if node_class.shape != (n,) or node_class.max(initial=0) > 3:
+        raise ValueError("node_class must hold one class 0..3 per row")
+    pat, reps, base = dedup_rows(csr)
+
+    # alias tables per exact pattern, then a second dedup on the QUANTISED tables: rows that differ
+    # only in the last fp64 bits of the reference's pairwise normalisation (54 bit
+    # patterns for 31 structural ones at the defaults) draw from identical 32-bit tables.
+    merged: dict = {}
+    merged_of = np.zeros(len(reps), dtype=np.int64)
+    th_all, a_all, b_all, sizes = [], [], [], []
+    max_rel = 0
+    for pi, r in enumerate(reps):
+        lo, hi = int(csr.indptr[r]), int(csr.indptr[r + 1])
+        rel = csr.cols[lo:hi].astype(np.int64) - int(csr.cols[lo])
+        prob, alias = _vose(csr.vals[lo:hi])
+        k = np.rint(prob * 4294967296.0).astype(np.int64)      # P(own) = k / 2^32
+        k = np.clip(k, 0, 4294967296)
+        a = rel.copy()
+        b = rel[alias]
+        never = k == 0
+        a[never] = b[never]                                    # coin can never pick "own"
+        th = np.where(never, 0, k - 1).astype(np.uint32)       # own  <=>  r1 <= th
+        key = (th.tobytes(), a.tobytes(), b.tobytes())
+        mi = merged.get(key)
+        if mi is None:
+            mi = len(sizes)
+            merged[key] = mi
+            th_all.append(th); a_all.append(a); b_all.append(b); sizes.append(hi - lo)
+            max_rel = max(max_rel, int(rel.max()))
+        merged_of[pi] = mi
+    offs = np.zeros(len(sizes) + 1, dtype=np.int64)
+    offs[1:] = np.cumsum(sizes)
+    pat = np.where(pat >= 0, merged_of[np.maximum(pat, 0)], -1)
+    n_patterns = len(sizes)
+    n_alias = int(offs[-1])
+    th_all = np.concatenate(th_all) if th_all else np.zeros(0, np.uint32)
+    a_all = np.concatenate(a_all) if a_all else np.zeros(0, np.int64)
+    b_all = np.concatenate(b_all) if b_all else np.zeros(0, np.int64)
+
+    fits = (n_alias <= COMPACT_MAX_ENTRIES and int(lens.max(initial=0)) <= COMPACT_MAX_N
+            and max_rel <= COMPACT_MAX_REL)
+    if layout == "auto":
+        layout = "compact" if fits else "wide"
+    if layout == "compact" and not fits:
+        raise ValueError("matrix does not fit the compact alias layout "
+                         "(entries=%d, max row=%d, max relative column=%d)"
+                         % (n_alias, int(lens.max(initial=0)), max_rel))
+
+    row_off = np.where(pat >= 0, offs[np.maximum(pat, 0)], 0).astype(np.uint32)
+    row_n = lens.astype(np.uint32)
+    row_n[csr.n_live:] = 0                                     # rows >= n_live are never stepped
+    row_base = base.astype(np.uint32)
+    if layout == "compact":
+        w0 = row_off | (row_n << np.uint32(20)) | (node_class << np.uint32(30))
+        rowinfo = np.stack([w0, row_base], axis=1).astype(np.uint32)
+        ab = (a_all.astype(np.uint32) & np.uint32(0xFFFF)) | (b_all.astype(np.uint32) << np.uint32(16))
+        alias = np.stack([th_all, ab], axis=1).astype(np.uint32)
+        if alias.shape[0] == 0:
+            alias = np.zeros((1, 2), np.uint32)
+    else:
+        rowinfo = np.stack([row_off, row_n, row_base, node_class], axis=1).astype(np.uint32)
+        alias = np.stack([th_all, a_all.astype(np.uint32), b_all.astype(np.uint32),
+                          np.zeros(n_alias, np.uint32)], axis=1).astype(np.uint32)
+        if alias.shape[0] == 0:
+            alias = np.zeros((1, 4), np.uint32)
+    return AliasTables(layout=layout, rowinfo=np.ascontiguousarray(rowinfo),
+                       alias=np.ascontiguousarray(alias), n_patterns=n_patterns,
+                       pattern_of_row=pat)
+
+
+def alias_row_distribution(csr: TransitionCSR, at: AliasTables, row: int) -> dict:
+    """Exact distribution the device draws from for ``row`` (for tests): {column: probability}."""
+    if at.layout == "compact":
+        w0, base = int(at.rowinfo[row, 0]), int(at.rowinfo[row, 1])
+        off, n = w0 & 0xFFFFF, (w0 >> 20) & 0x3FF
+    else:
+        off, n, base = (int(x) for x in at.rowinfo[row, :3])
+    out: dict = {}
+    for s in range(n):
+        e = at.alias[off + s]
+        if at.layout == "compact":
+            th, a, b = int(e[0]), int(e[1]) & 0xFFFF, int(e[1]) >> 16
+        else:
+            th, a, b = int(e[0]), int(e[1]), int(e[2])
+        p_own = (th + 1) / 4294967296.0
+        out[base + a] = out.get(base + a, 0.0) + p_own / n
+        out[base + b] = out.get(base + b, 0.0) + (1.0 - p_own) / n
+    return {k: v for k, v in out.items() if v > 0}
+
+
+def classify_source(srcvals: np.ndarray, n_rows: int):
+    """Map per-node source values to <= 3 non-zero classes: (node_class uint8[n_rows],
+    class_value float64[4]).  The fused score tally adds class_value[class(node)] per visit."""
+    vals = np.unique(srcvals[srcvals != 0])
+    if len(vals) > 3:
+        raise ValueError("the fused score tally supports at most 3 distinct non-zero source "
+                         "values (got %d); use the occupancy tally instead" % len(vals))
+    node_class = np.zeros(n_rows, dtype=np.uint8)
+    class_value = np.zeros(4)
+    for ci, x in enumerate(vals, start=1):
+        node_class[:len(srcvals)][srcvals == x] = ci
+        class_value[ci] = x
+    return node_class, class_value
