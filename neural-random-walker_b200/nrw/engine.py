@@ -154,6 +154,29 @@ class ReplayResult:
     draws_used: int
 
 
+class PreparedWalk:
+    """A K1 launch descriptor built once: ``pw()`` re-zeroes the tallies and launches again,
+    ``pw.launch_kernel()`` launches without touching the tallies (what bench.py times)."""
+
+    def __init__(self, engine, tables, wstruct, res):
+        self.engine, self.tables, self.w, self.res = engine, tables, wstruct, res
+        self.tallies = [t for t in (res.counters, res.score, res.score_sq, res.node_hist, res.count_tn)
+                        if t is not None]
+
+    def zero(self):
+        for t in self.tallies:
+            t.zero_()
+
+    def launch_kernel(self):
+        e = self.engine
+        e._check(e.lib.nrw_walk_philox(e.handle, C.byref(self.tables.struct), C.byref(self.w), e.stream))
+
+    def __call__(self):
+        self.zero()
+        self.launch_kernel()
+        return self.res
+
+
 class Engine:
     """One engine per (process, device).  All launches go to torch's current stream."""
 
@@ -195,8 +218,10 @@ class Engine:
         return C.c_void_p(self.torch.cuda.current_stream(self.device).cuda_stream)
 
     def _dev(self, arr, dtype):
-        t = self.torch.from_numpy(np.ascontiguousarray(arr, dtype=dtype))
-        return t.to(self.device)
+        a = np.ascontiguousarray(arr, dtype=dtype)
+        if not a.flags.writeable:
+            a = a.copy()
+        return self.torch.from_numpy(a).to(self.device)
 
     # ------------------------------------------------------------------ tables
     def upload(self, csr: TransitionCSR, node_class=None, alias=True, alias_layout="auto") -> DeviceTables:
@@ -322,15 +347,7 @@ class Engine:
         res.kernel = name.value.decode()
         res._keep = keep
         res.launch_geometry = (grid.value, block.value, smem.value)
-        tallies = [t for t in (res.counters, res.score, res.score_sq, res.node_hist, res.count_tn)
-                   if t is not None]
-
-        def launch():
-            for t in tallies:
-                t.zero_()
-            self._check(self.lib.nrw_walk_philox(self.handle, C.byref(tables.struct), C.byref(w), self.stream))
-            return res
-        return launch, res
+        return PreparedWalk(self, tables, w, res), res
 
     # ------------------------------------------------------------------ K2
     def replay(self, tables: DeviceTables, start_nodes, start_counts, nt, *, draw=None,

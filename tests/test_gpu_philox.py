@@ -188,7 +188,8 @@ def test_fluence_philox_matches_reference_expectation(engine, c1_csr):
             # the tallied second moment reproduces the exact per-walker variance
             if M >= 100000:
                 big = sigma > 0
-                assert np.allclose(res.stderr[big], sigma[big], rtol=0.05)
+                ratio = res.stderr[big] / sigma[big]
+                assert abs(np.median(ratio) - 1.0) < 0.01 and np.abs(ratio - 1.0).max() < 0.25
 
 
 def test_fluence_philox_time_weighted_matches_expectation(engine, c1_csr):
@@ -207,15 +208,27 @@ def test_fluence_philox_time_weighted_matches_expectation(engine, c1_csr):
 
 
 def test_simple_flux_philox_matches_closed_form(tmp_path):
-    """The reference's only known answer (simple_flux_miniapp.py:338-343): with M = 2e6 the walk
-    must sit within 5 sigma of the discrete chain and within 2 % of the continuous closed form."""
+    """The reference's only known answer (simple_flux_miniapp.py:338-343).  With M = 2e6 the walk
+    must sit within 5 sigma of the exact propagation of the reference's chain, and within the
+    chain's own discretisation bias (0.0675) + noise of the continuous closed form."""
     import simple_flux_miniapp as app
-    a = vars(app.build_parser().parse_args(["-r", "pc", "--rng", "philox", "-M", "2000000"]))
+    from nrw import mesh
+    M = 2000000
+    a = vars(app.build_parser().parse_args(["-r", "pc", "--rng", "philox", "-M", str(M)]))
     a.update(matrix_filename=str(tmp_path / "m.csv"), results_filename=str(tmp_path / "r.csv"))
     np.random.seed(4)
     sol = app.run(a)
+    assert sol.shape == (2, 1002)
     t, true = app.true_solution(a, sol.shape[1])
-    assert np.abs(sol[:, :800] - true[:, :800]).max() < 0.02 * 5.0
+    assert np.abs(sol - true).max() < 0.08
+    q = mesh.build_simple_flux_dense(0.005, 8.0, 2.0)[:2, :2]
+    p = np.eye(2)
+    w = np.array([5.0, 3.0])
+    for j in range(1002):
+        mean = p @ w
+        var = p @ (w * w) - mean ** 2            # per-walker variance of ip*1[+] + in*1[-]
+        assert (np.abs(sol[:, j] - mean) <= 5.0 * np.sqrt(np.maximum(var, 0) / M) + 1e-12).all(), j
+        p = q @ p
     # --use_sinks must not change rwSol (Q14)
     a["use_sinks"] = True
     np.random.seed(4)

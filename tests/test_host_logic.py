@@ -1,0 +1,281 @@
+"""CPU tests of the product's host logic (no GPU, no compute calls into libnrw):
+mesh builder bit-exactness, matrix files, sampling tables, index maps, CLI surface, sharding."""
+import os
+import re
+
+import numpy as np
+import pytest
+
+from conftest import C1, ROOT
+from nrw import dist, mesh, tables
+from oracle import philox_port, ref_import, restated as R
+
+
+# ---------------------------------------------------------------- builder
+def test_pairwise_rowsum_emulation_matches_numpy():
+    rng = np.random.default_rng(0)
+    for n in (1, 5, 8, 9, 100, 128, 129, 901, 1000, 10001, 158761):
+        for _ in range(12):
+            W = int(rng.integers(1, min(n, 130) + 1))
+            c0 = int(rng.integers(0, n - W + 1))
+            block = rng.random((4, W))
+            dense = np.zeros((4, n))
+            dense[:, c0:c0 + W] = block
+            assert np.array_equal(dense.sum(axis=1), mesh._pairwise_rowsum_window(n, c0, block))
+
+
+def test_csr_builder_is_bit_identical_to_reference_matrix(c1_csr, golden):
+    g = golden["fluence_c1_matrix"]
+    assert c1_csr.n_rows == 901 and c1_csr.n_live == 900 and c1_csr.nnz == 13950
+    assert np.array_equal(c1_csr.indptr, g["indptr"]) and np.array_equal(c1_csr.cols, g["cols"])
+    assert np.array_equal(c1_csr.vals.view(np.uint64), g["vals"].view(np.uint64))
+
+
+@pytest.mark.parametrize("dt,da", [(0.01, 0.02), (0.0025, 1.0 / 16.0), (0.005, 1.0 / 15.0)])
+def test_csr_builder_matches_oracle_dense_on_other_meshes(dt, da):
+    csr = mesh.build_fluence_csr(dt, da, 200, 0.15, 1)
+    q, m = R.fluence_matrix_dense(dt, da, 200, 0.15, 1)
+    assert np.array_equal(csr.to_dense(), q)
+    assert csr.n_live == m["meshSize"]
+
+
+def test_refined_mesh_shape():
+    """BASELINE config C4: 1260 x 126 nodes -- the reference cannot even allocate this matrix."""
+    csr = mesh.build_fluence_csr(0.001, 1.0 / 63.0, 200, 0.15, 1)
+    m = csr.meta["mesh"]
+    assert (m["NS"] - 1, m["ND"] - 1, csr.n_live) == (1260, 126, 158760)
+    assert np.all(np.abs(np.add.reduceat(csr.vals, csr.indptr[:-2]) - 1) < 1e-12)
+
+
+def test_bad_physics_raises_like_the_reference():
+    with pytest.raises(ValueError, match="too large"):
+        mesh.build_fluence_csr(0.05, 1.0 / 15.0, 200, 0.15, 1)       # fluence_mini_app.py:285-291
+    with pytest.raises(ValueError, match="too large"):
+        mesh.build_simple_flux_dense(0.05, 8.0, 2.0)                 # simple_flux_miniapp.py:232-238
+    with pytest.raises(IndexError):
+        mesh.build_fluence_csr(0.01, 0.07, 200, 0.15, 1)             # steps miss cell centres (Q15)
+
+
+def test_simple_flux_matrix(golden):
+    q = mesh.build_simple_flux_dense(0.005, 8.0, 2.0)
+    assert np.array_equal(q, golden["simple_flux"]["myQ"])
+    csr = mesh.csr_from_dense(q, n_live=2)
+    assert csr.row_lengths().tolist() == [3, 3, 0]
+
+
+def test_matrix_csv_is_byte_identical_to_savetxt_and_round_trips(tmp_path, c1_csr):
+    a, b = str(tmp_path / "a.csv"), str(tmp_path / "b.csv")
+    mesh.save_matrix_csv(a, c1_csr)
+    np.savetxt(b, c1_csr.to_dense(), delimiter=",")
+    assert open(a, "rb").read() == open(b, "rb").read()
+    back = mesh.load_matrix(a, n_live=900)
+    assert np.array_equal(back.vals.view(np.uint64), c1_csr.vals.view(np.uint64))
+    assert np.array_equal(back.cols, c1_csr.cols) and np.array_equal(back.indptr, c1_csr.indptr)
+    assert mesh.load_matrix(a, n_live=900) is back                   # cached, not re-parsed
+    z = str(tmp_path / "m.npz")
+    mesh.save_matrix_npz(z, c1_csr)
+    assert np.array_equal(mesh.load_matrix(z).vals, c1_csr.vals)
+
+
+# ---------------------------------------------------------------- tables
+def test_row_cum_equals_dense_cumsum(c1_csr):
+    cum = tables.row_cum(c1_csr)
+    dense = np.cumsum(c1_csr.to_dense(), axis=1)
+    rows = np.repeat(np.arange(c1_csr.n_rows), c1_csr.row_lengths())
+    assert np.array_equal(cum, dense[rows, c1_csr.cols])
+    assert (cum[c1_csr.indptr[1:-1] - 1] < 1).sum() == 416           # 416 rows end below 1
+
+
+@pytest.mark.parametrize("layout", ["compact", "wide"])
+def test_alias_tables_reproduce_row_probabilities(c1_csr, layout):
+    at = tables.build_alias(c1_csr, layout=layout)
+    assert at.n_patterns == 31 and at.n_alias == 901                 # 30 stay patterns + the exit row
+    for r in list(range(0, 900, 37)) + [899]:
+        d = tables.alias_row_distribution(c1_csr, at, r)
+        lo, hi = c1_csr.indptr[r], c1_csr.indptr[r + 1]
+        p = c1_csr.vals[lo:hi] / c1_csr.vals[lo:hi].sum()
+        assert set(d) == set(c1_csr.cols[lo:hi].tolist())
+        assert max(abs(d[int(c)] - x) for c, x in zip(c1_csr.cols[lo:hi], p)) < 2e-10   # 2^-32 coin
+    assert tables.alias_row_distribution(c1_csr, at, 900) == {}      # sink: never stepped
+
+
+def test_alias_on_arbitrary_sparse_graph():
+    """Ragged rows, an absorbing row in the middle, a zero row, a row with one huge and many tiny
+    probabilities -- the densityrw-style generic graph."""
+    rng = np.random.default_rng(3)
+    n = 40
+    q = np.zeros((n, n))
+    for r in range(n - 1):
+        k = int(rng.integers(1, 9))
+        c = rng.choice(n, size=k, replace=False)
+        w = rng.random(k) ** 4
+        q[r, c] = w / w.sum()
+    q[7] = 0
+    q[11] = 0
+    q[11, 3] = 1.0
+    csr = mesh.csr_from_dense(q, n_live=n - 1)
+    for layout in ("compact", "wide"):
+        at = tables.build_alias(csr, layout=layout)
+        for r in range(n):
+            d = tables.alias_row_distribution(csr, at, r)
+            if r >= n - 1 or r == 7:
+                assert d == {}
+                continue
+            ref = {int(c): float(x) for c, x in zip(np.nonzero(q[r])[0], q[r][np.nonzero(q[r])])}
+            assert set(d) <= set(ref)
+            assert max(abs(d.get(c, 0.0) - x) for c, x in ref.items()) < 2e-9
+
+
+def test_compact_layout_limits():
+    q = np.zeros((3, 70000))
+    q = np.zeros((70001, 70001))
+    q[0, 0] = 0.5
+    q[0, 70000] = 0.5
+    csr = mesh.csr_from_dense(q)
+    assert tables.build_alias(csr).layout == "wide"                  # relative column > 65535
+    with pytest.raises(ValueError):
+        tables.build_alias(csr, layout="compact")
+
+
+def test_classify_source(c1_csr):
+    m = c1_csr.meta["mesh"]
+    for src_fn, val in ((mesh.source_default, 3.0), (mesh.source_paper, 0.015)):
+        src = mesh.source_values(m["meshpoints"], src_fn)
+        nc, cv = tables.classify_source(src, c1_csr.n_rows)
+        assert cv.tolist() == [0.0, val, 0.0, 0.0] and nc[900] == 0
+        assert np.array_equal(nc[:900] == 1, src != 0)
+    with pytest.raises(ValueError):
+        tables.classify_source(np.arange(10.0), 11)
+
+
+# ---------------------------------------------------------------- index maps / sources
+def test_scatter_to_rwsol_reproduces_the_reference_index_quirk():
+    from nrw.fluence import scatter_to_rwsol
+    NS, ND = 31, 31
+    per = np.arange(900, dtype=np.float64) + 1
+    ref = np.zeros((30, 30))
+    for i in range(900):
+        p, a = R.result_index(i, ND)
+        ref[p, a] = per[i]
+    got = scatter_to_rwsol(per, NS, ND)
+    assert np.array_equal(got, ref)
+    assert got[0, 29] == 31 and got[29, 29] == 0
+    assert mesh.result_index(0, ND) == R.result_index(0, ND) == (0, 29)
+
+
+def test_source_terms():
+    for x, y in ((0.1, 0.0), (0.3, -0.2), (0.0, 0.05859375), (0.0, 0.0586), (-0.5, 0.3)):
+        assert mesh.source_default(x, y) == R.source_term_default(x, y)
+        assert mesh.source_paper(x, y) == R.source_term_paper(x, y)
+
+
+def test_exp_time_weights_are_scalar_exp():
+    from nrw.dropin import exp_time_weights
+    w = exp_time_weights(0.7, 0.01, 300)
+    assert all(w[j] == np.exp(-0.7 * 0.01 * j) for j in range(300))
+    assert np.array_equal(exp_time_weights(0, 0.01, 5), np.ones(5))
+
+
+# ---------------------------------------------------------------- CLI surface
+def _ref_cli(path):
+    """(flags, default-repr, help) triples parsed from the reference's add_argument lines."""
+    src = open(path).read()
+    out = {}
+    for m in re.finditer(r"parser\.add_argument\((.*)\)\n", src):
+        body = m.group(1)
+        flags = tuple(re.findall(r"'(-{1,2}[A-Za-z_]+)'", body.split("help")[0].split("default")[0]))
+        h = re.search(r"help=(['\"])(.*)\1", body)
+        out[flags] = h.group(2) if h else None
+    return out
+
+
+@pytest.mark.skipif(not ref_import.reference_available(), reason="reference not mounted")
+@pytest.mark.parametrize("name", ["fluence_mini_app", "simple_flux_miniapp"])
+def test_cli_matches_reference_flags_defaults_and_help(name):
+    import importlib
+    app = importlib.import_module(name)
+    ours = {flags: kw for flags, kw in app.CLI}
+    ref = _ref_cli(os.path.join(ref_import.REFERENCE_ROOT, name + ".py"))
+    assert len(ref) >= 18
+    for flags, help_ in ref.items():
+        assert flags in ours, flags
+        assert ours[flags].get("help") == help_, flags
+    refargs = (ref_import.fluence_default_args() if name == "fluence_mini_app"
+               else ref_import.simple_flux_default_args())
+    got = vars(app.build_parser().parse_args([]))
+    for k, v in refargs.items():
+        if k == "run_mode":
+            assert got[k] == "fugu"                                   # the reference's default mode
+        else:
+            assert got[k] == v, k
+    added = set(got) - set(refargs)
+    assert added <= {"rng", "source", "sampler"}                      # additive flags only
+
+
+def test_dispatch_table_keeps_the_reference_modes():
+    import fluence_mini_app as f
+    import simple_flux_miniapp as s
+    for app in (f, s):
+        assert set(app.run_functions) == {"fugu", "loihi", "spinnaker", "pc"}
+        assert app.run_functions["pc"] is app.run_pc
+        with pytest.raises(NotImplementedError, match="-r pc"):
+            app.run_functions["loihi"](matrix_filename="m", neuraltime=1, initial_walkers=[[0, 1]], meshSize=1)
+
+
+def test_pc_mode_fails_loudly_without_a_gpu(tmp_path, c1_csr):
+    """No CPU fallback: on a machine without CUDA the pc back end raises, it does not emulate."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    import fluence_mini_app as app
+    from nrw.engine import NrwError
+    p = str(tmp_path / "m.csv")
+    mesh.save_matrix_csv(p, c1_csr)
+    with pytest.raises(NrwError, match="no CPU fallback"):
+        app.run_pc(matrix_filename=p, neuraltime=8, initial_walkers=[[0, 5]], meshSize=900)
+
+
+# ---------------------------------------------------------------- sharding / device-sampler port
+def test_shard_range_partitions_exactly():
+    for total in (0, 1, 7, 100, 12500, 10 ** 9 + 7):
+        for world in (1, 2, 3, 8):
+            for align in (1, 32):
+                spans = [dist.shard_range(total, r, world, align) for r in range(world)]
+                assert spans[0][0] == 0 and spans[-1][1] == total
+                assert all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
+                assert all(lo <= hi for lo, hi in spans)
+
+
+def test_philox_known_answers():
+    """Random123 known-answer vectors for Philox2x32-10."""
+    kat = [((0x00000000, 0x00000000), 0x00000000, (0xff1dae59, 0x6cd10df2)),
+           ((0xffffffff, 0xffffffff), 0xffffffff, (0x2c3f628b, 0xab4fd7ad)),
+           ((0x243f6a88, 0x85a308d3), 0x13198a2e, (0xdd7ce038, 0xf62a4c12))]
+    for (c0, c1), key, (e0, e1) in kat:
+        r0, r1 = philox_port.philox2x32_10(np.array([c0]), np.array([c1]), key)
+        assert (int(r0[0]), int(r1[0])) == (e0, e1)
+
+
+def test_port_sharding_invariance_and_statistics(c1_csr):
+    """The device-sampler port itself: slices with start_id_base sum to the unsharded tallies, and
+    its mean score agrees with the reference chain's expectation."""
+    from oracle import expectation
+    src = mesh.source_values(c1_csr.meta["mesh"]["meshpoints"], mesh.source_default)
+    nc, cv = tables.classify_source(src, c1_csr.n_rows)
+    at = tables.build_alias(c1_csr, node_class=nc)
+    starts, M, nt, seed = np.arange(0, 900, 9), 400, 64, 3
+    full = philox_port.walk_port(c1_csr, starts, M, nt, seed, alias=at, class_value=[0, 1, 0, 0],
+                                 start_id_base=starts * M)
+    acc = np.zeros_like(full["score"])
+    for rank in range(2):
+        lo, hi = dist.shard_range(M, rank, 2)
+        part = philox_port.walk_port(c1_csr, starts, hi - lo, nt, seed, alias=at, class_value=[0, 1, 0, 0],
+                                     start_id_base=starts * M + lo)
+        acc += part["score"]
+    assert np.array_equal(acc, full["score"])
+    mean, var = expectation.fluence_moments(c1_csr.indptr, c1_csr.cols, c1_csr.vals, 901, 900, src, nt,
+                                            0.0, C1["dt"], C1["v"])
+    est = full["score"] * 3.0 * C1["v"] * C1["dt"] / M
+    sig = np.sqrt(var[starts] / M)
+    z = np.abs(est - mean[starts]) / np.where(sig > 0, sig, 1)
+    assert z.max() < 4.5 and (est[sig == 0] == mean[starts][sig == 0]).all()
