@@ -103,7 +103,7 @@ typedef struct nrw_walk {
     /* per-start score tally (fused fluence_mini_app.py:428-434): for every step
      * 1 <= t <= nt-2 that lands on a live node k, the walker's score grows by
      * llrint(time_weight[t] * class_value[cls(k)])  (time_weight NULL => 1.0, in which
-     * case class_value must hold integers).  score[s] += sum over the start's walkers,
+     * case class_value must hold integers in [0, 255]).  score[s] += sum over the start's walkers,
      * score_sq[s] += sum of squared per-walker scores (for the 3-sigma test).           */
     int64_t* score;                 /* [n_starts] or NULL                                */
     double*  score_sq;              /* [n_starts] or NULL                                */

@@ -193,12 +193,16 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
     p.lo = w->walker_lo; p.hi = w->walker_hi;
     p.key = seed_to_key(w->seed); p.nt = w->nt;
     p.score = (long long*)w->score; p.score_sq = w->score_sq; p.tw = w->time_weight;
+    p.cwpack = 0;
     for (int i = 0; i < 4; ++i) {
         p.cv[i] = w->class_value[i];
-        p.cw[i] = (long long)w->class_value[i];
-        if (!w->time_weight && w->score && (double)p.cw[i] != w->class_value[i])
-            return fail(NRW_EINVAL, "nrw_walk_philox: class_value[%d]=%g must be an integer when "
-                        "time_weight is NULL", i, w->class_value[i]);
+        if (!w->time_weight && w->score) {
+            const long long q = (long long)w->class_value[i];
+            if ((double)q != w->class_value[i] || q < 0 || q > 255)
+                return fail(NRW_EINVAL, "nrw_walk_philox: class_value[%d]=%g must be an integer in "
+                            "[0, 255] when time_weight is NULL", i, w->class_value[i]);
+            p.cwpack |= (uint32_t)q << (8 * i);
+        }
     }
     p.node_hist = w->node_hist; p.count_tn = w->count_tn;
     p.t_cap = w->t_cap; p.per_start = w->count_per_start;

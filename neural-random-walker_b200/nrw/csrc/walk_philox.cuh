@@ -18,6 +18,8 @@
 //     time-resolved counts (tempdata) in shared memory with __match_any_sync aggregation or in
 //     global memory.
 #pragma once
+#include <type_traits>
+
 #include "common.cuh"
 
 namespace nrw {
@@ -35,7 +37,7 @@ struct WalkParams {
     long long lo, hi;
     uint32_t key; int nt;
     long long* score; double* score_sq;
-    long long cw[4]; double cv[4]; const double* tw;
+    uint32_t cwpack; double cv[4]; const double* tw;
     unsigned long long* node_hist;
     uint32_t* count_tn; int t_cap; int per_start; int cnt_bins;
     unsigned long long* counters;
@@ -125,22 +127,27 @@ walk_philox_kernel(const __grid_constant__ WalkParams p) {
     const uint32_t key = p.key;
     const int t_last = p.nt - 1;        // last model step (fluence_mini_app.py:236)
     const int t_score_max = p.nt - 2;   // solution sum skips the final step (:428, Q3)
+    using ScoreT = typename std::conditional<(TL & TL_TW) != 0, long long, uint32_t>::type;
 
-    // ---- lane state ------------------------------------------------------------------------------
-    bool alive = false;
-    uint32_t c0 = 0, chi = 0;           // Philox counter: walker id (low 32 | bits 32..39 << 24)
-    int t = 0;
+    // ---- lane state (32-bit wherever the range allows: the loop is issue-bound) ------------------
+    int t = -1;                         // steps taken by the lane's walker; -1 = no walker
+    uint32_t c0 = 0, chi = 0;           // Philox counter: stream id (low 32 | bits 32..39 << 24)
     RowRegs<TAB> row{0, 0, 0, 0};
-    long long x = 0;                    // this walker's score
+    ScoreT x = 0;                       // this walker's score
     int s = -1;                         // start index the lane is accumulating for
-    long long s_lo = 0, s_end = 0, s_idoff = 0;   // stream id = g + s_idoff
+    long long s_end = 0;                // global id at which start s ends
+    uint32_t s_end_off = 0;             // the same, as an offset into the warp's current range
+    long long sid_base = 0;             // stream id of offset 0 of the current range within start s
+    int t_init = 0; uint32_t surv_init = 0;   // state of a fresh walker of start s (dead if absorbing)
     RowRegs<TAB> srow{0, 0, 0, 0};
     long long acc = 0; double acc2 = 0.0;
-    unsigned long long nsteps = 0;
-    uint32_t nexit = 0, nsurv = 0, nwalk = 0, novf = 0, sinkc = 0;
-    // warp-uniform
-    long long cursor = 0, range_end = 0;
+    uint32_t nsteps = 0, nsurv = 0, novf = 0, sinkc = 0;
+    // warp-uniform: the warp's current id range is [rbase + cur, rbase + end)
+    long long rbase = 0;
+    uint32_t cur = 0, end = 0;
+    unsigned long long wwalk = 0;       // walkers taken by this warp (sum of range lengths)
     bool exhausted = false;
+    const uint32_t lt_mask = lanemask_lt();
 
     auto flush_score = [&]() {
         if constexpr (TL & TL_SCORE) {
@@ -152,30 +159,46 @@ walk_philox_kernel(const __grid_constant__ WalkParams p) {
             acc = 0; acc2 = 0.0;
         }
     };
+    // offset (clamped to 2^31) of the end of start s inside the current range
+    auto rel_end = [&]() -> uint32_t {
+        const long long d = s_end - rbase;
+        return d <= 0 ? 0u : (d > 0x7fffffffll ? 0x7fffffffu : (uint32_t)d);
+    };
 
     while (true) {
-        // ---- refill dead lanes (warp vote ranks them) ---------------------------------------
-        const unsigned need = __ballot_sync(NRW_FULL_MASK, !alive);
+        // ---- refill dead lanes (warp vote ranks them; ids only ever grow for a lane) ---------
+        const unsigned need = __ballot_sync(NRW_FULL_MASK, t < 0);
         if (need) {
-            if (cursor >= range_end && !exhausted) {
-                long long a = 0;
-                if (lane == 0) a = (long long)atomicAdd(p.work_next, (unsigned long long)p.range);
-                a = __shfl_sync(NRW_FULL_MASK, a, 0);
-                cursor = p.lo + a;
-                if (cursor >= p.hi) { exhausted = true; cursor = range_end = p.hi; }
-                else range_end = min(cursor + p.range, p.hi);
+            if (cur >= end) {
+                if (!exhausted) {
+                    long long a = 0;
+                    if (lane == 0) a = (long long)atomicAdd(p.work_next, (unsigned long long)p.range);
+                    a = __shfl_sync(NRW_FULL_MASK, a, 0);
+                    const long long nb = p.lo + a;
+                    cur = 0;
+                    if (nb >= p.hi) { exhausted = true; end = 0; }
+                    else {
+                        end = (uint32_t)min(p.range, p.hi - nb);
+                        wwalk += end;
+                        sid_base += nb - rbase;                  // same start, new range origin
+                        rbase = nb;
+                        s_end_off = rel_end();
+                    }
+                }
+                if (exhausted && !__any_sync(NRW_FULL_MASK, t >= 0)) break;
             }
-            const int rank = __popc(need & lanemask_lt());
-            const long long gnew = cursor + rank;
-            const bool take = !alive && gnew < range_end;
-            cursor = min(cursor + (long long)__popc(need), range_end);
+            const uint32_t off = cur + (uint32_t)__popc(need & lt_mask);
+            const bool take = (t < 0) && (off < end);
+            cur = min(cur + (uint32_t)__popc(need), end);
             if (take) {
-                if (gnew >= s_end || gnew < s_lo) {
+                if (off >= s_end_off) {                           // next start (cold path)
+                    const long long gnew = rbase + (long long)off;
                     flush_score();
+                    long long s_lo = s_end;
                     bool found = false;
-                    if (s >= 0 && gnew >= s_end && s + 1 < p.n_starts) {
+                    if (s >= 0 && s + 1 < p.n_starts) {
                         const long long e2 = __ldg(p.start_prefix + s + 2);
-                        if (gnew < e2) { ++s; s_lo = s_end; s_end = e2; found = true; }
+                        if (gnew < e2) { ++s; s_end = e2; found = true; }
                     }
                     if (!found) {
                         int lo_i = 0, hi_i = p.n_starts;
@@ -188,25 +211,23 @@ walk_philox_kernel(const __grid_constant__ WalkParams p) {
                         s_end = __ldg(p.start_prefix + s + 1);
                     }
                     srow = load_row<TAB>(p, rowinfo_s, __ldg(p.start_nodes + s));
-                    s_idoff = p.start_id_base ? (__ldg(p.start_id_base + s) - s_lo) : 0ll;
+                    sid_base = rbase + (p.start_id_base ? (__ldg(p.start_id_base + s) - s_lo) : 0ll);
+                    s_end_off = rel_end();
+                    const bool absorbing = row_n<TAB>(srow) == 0u;   // started on the sink: an exit
+                    t_init = (absorbing || t_last < 1) ? -1 : 0;
+                    surv_init = (!absorbing && t_last < 1) ? 1u : 0u;
                 }
                 row = srow;
-                const unsigned long long sid = (unsigned long long)(gnew + s_idoff);
+                const unsigned long long sid = (unsigned long long)(sid_base + (long long)off);
                 c0 = (uint32_t)sid;
                 chi = (uint32_t)(sid >> 32) << 24;
-                t = 0; x = 0;
-                ++nwalk;
-                alive = (row_n<TAB>(row) > 0u) && (t_last >= 1);
-                if (!alive) { if (row_n<TAB>(row) == 0u) ++nexit; else ++nsurv; }
+                t = t_init; x = 0;
+                nsurv += surv_init;
             }
-        }
-        if (!__any_sync(NRW_FULL_MASK, alive)) {
-            if (exhausted) break;
-            continue;
         }
 
         // ---- one model step for every live lane ---------------------------------------------
-        const bool stepped = alive;
+        const bool stepped = t >= 0;
         int knew = 0;
         if (stepped) {
             ++t; ++nsteps;
@@ -235,7 +256,7 @@ walk_philox_kernel(const __grid_constant__ WalkParams p) {
                     const double cvv = cls == 0 ? p.cv[0] : cls == 1 ? p.cv[1] : cls == 2 ? p.cv[2] : p.cv[3];
                     x += __double2ll_rn(__ldg(p.tw + t) * cvv);
                 } else {
-                    x += cls == 0 ? p.cw[0] : cls == 1 ? p.cw[1] : cls == 2 ? p.cw[2] : p.cw[3];
+                    x += (p.cwpack >> (cls * 8u)) & 0xffu;        // byte-packed integer class weights
                 }
             }
         }
@@ -271,10 +292,10 @@ walk_philox_kernel(const __grid_constant__ WalkParams p) {
         if (stepped) {
             const bool absorbed = row_n<TAB>(row) == 0u;
             if (absorbed || t >= t_last) {
-                alive = false;
-                if (absorbed) ++nexit; else ++nsurv;
+                if (!absorbed) ++nsurv;
+                t = -1;
                 if constexpr (TL & TL_SCORE) {
-                    acc += x;
+                    acc += (long long)x;
                     if (p.score_sq) { const double xd = (double)x; acc2 += xd * xd; }
                 }
             }
@@ -290,21 +311,20 @@ walk_philox_kernel(const __grid_constant__ WalkParams p) {
         }
     }
     unsigned long long v0 = nsteps;
-    uint32_t v1 = nexit, v2 = nsurv, v3 = novf, v4 = nwalk;
+    uint32_t v2 = nsurv, v3 = novf;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
         v0 += __shfl_xor_sync(NRW_FULL_MASK, v0, o);
-        v1 += __shfl_xor_sync(NRW_FULL_MASK, v1, o);
         v2 += __shfl_xor_sync(NRW_FULL_MASK, v2, o);
         v3 += __shfl_xor_sync(NRW_FULL_MASK, v3, o);
-        v4 += __shfl_xor_sync(NRW_FULL_MASK, v4, o);
     }
+    const unsigned long long v4 = wwalk, v1 = wwalk - v2;          // exits = walkers - survivors
     if (lane == 0 && p.counters) {
         if (v0) atomicAdd(p.counters + 0, v0);
-        if (v1) atomicAdd(p.counters + 1, (unsigned long long)v1);
+        if (v1) atomicAdd(p.counters + 1, v1);
         if (v2) atomicAdd(p.counters + 2, (unsigned long long)v2);
         if (v3) atomicAdd(p.counters + 3, (unsigned long long)v3);
-        if (v4) atomicAdd(p.counters + 4, (unsigned long long)v4);
+        if (v4) atomicAdd(p.counters + 4, v4);
     }
     if constexpr (TL & (TL_HIST_S | TL_CNT_S)) {
         __syncthreads();
