@@ -59,8 +59,12 @@ def run_pc(matrix_filename=None, neuraltime=None, initial_walkers=None, meshSize
                               sampler=runtime_args.get('sampler', 'alias'))
 
 
-run_fugu = dropin.unavailable_backend('fugu', 'the Fugu spiking simulator (densityrw + Fugu)')
-run_loihi = dropin.unavailable_backend('loihi', "Intel's NxSDK and a Loihi board")
+# The 'fugu' and 'loihi' entries keep the reference's adapters (fluence_mini_app.py:43-192) but sit
+# on this build's densityrw / loihirw surfaces, i.e. the walk runs on the GPU and is written out as
+# the spike table / spike probes those adapters decode.  (The command line still refuses
+# ``-r loihi`` without NxSDK, as the reference does, :527-533.)
+run_fugu = dropin.fugu_adapter
+run_loihi = dropin.loihi_adapter
 run_spinnaker = dropin.unavailable_backend('spinnaker', 'sPyNNaker and a SpiNNaker board')
 
 run_functions = {'fugu': run_fugu, 'loihi': run_loihi, 'spinnaker': run_spinnaker, 'pc': run_pc}
@@ -123,7 +127,9 @@ def run(args):
                                     runtime_args={'fugu_backend': args['fugu_backend'],
                                                   'use_sinks': args['use_sinks'],
                                                   'runclean': args['runclean'],
-                                                  'rand_seed': args['rand_seed']})
+                                                  'rand_seed': args['rand_seed'],
+                                                  'rng': args.get('rng'),
+                                                  'sampler': args.get('sampler', 'alias')})
             rw_logger.info('    mesh point: {}'.format(i))
             rw_logger.debug('        elapsed time: {}'.format(time.time() - t0))
             posind, aind = mesh.result_index(i, ND)

@@ -123,3 +123,83 @@ def simple_flux_default_args(**over):
              rand_seed=-1, use_sinks=False)
     a.update(over)
     return a
+
+
+# ------------------------------------------------------------------------------------------
+# the "next" surface: loihirw.rw_analysis / rw_core, densityrw.DensityRW
+# ------------------------------------------------------------------------------------------
+
+_STUB_MODULES = ("nxsdk", "nxsdk.api", "nxsdk.api.n2a", "nxsdk.api.enums", "nxsdk.api.enums.api_enums",
+                 "nxsdk.graph", "nxsdk.graph.monitor", "nxsdk.graph.monitor.probes",
+                 "fugu", "fugu.bricks", "fugu.scaffold", "fugu.backends")
+
+
+def _load_packaged(relpath: str, alias: str, evict=("densityrw", "loihirw")):
+    """Load one file of a reference sub-package with inert stand-ins for the proprietary / absent
+    imports it makes at module level (NxSDK, Fugu).  Only pure-NumPy functions of those files are
+    ever called (rw_analysis.process_outputs*, rw_core.get_probCircuitValues,
+    DensityRW.load_transitions / build_test_graph)."""
+    if not reference_available():
+        raise FileNotFoundError("reference not present at %s" % REFERENCE_ROOT)
+    _install_stubs()
+    added = []
+    for name in _STUB_MODULES:
+        if name not in sys.modules:
+            sys.modules[name] = types.ModuleType(name)
+            added.append(name)
+
+    class _Inert:
+        def __init__(self, *a, **k):
+            pass
+    sys.modules["fugu"].input_coding_types = []
+    for mod, attrs in (("fugu.bricks", ("Brick", "Vector_Input")), ("fugu.scaffold", ("Scaffold",)),
+                       ("fugu.backends", ("snn_Backend",))):
+        for a in attrs:
+            setattr(sys.modules[mod], a, _Inert)
+    saved_path = list(sys.path)
+    saved = {k: v for k, v in sys.modules.items() if k.split(".")[0] in evict}
+    for k in saved:
+        del sys.modules[k]
+    import numpy as _np
+    had_nan = hasattr(_np, "NaN")
+    if not had_nan:
+        _np.NaN = _np.nan                        # SpikingPDE.py:367,385 predates numpy 2
+    try:
+        sys.path.insert(0, REFERENCE_ROOT)
+        spec = importlib.util.spec_from_file_location(alias, os.path.join(REFERENCE_ROOT, relpath))
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+    finally:
+        sys.path[:] = saved_path
+        for k in [k for k in sys.modules if k.split(".")[0] in evict]:
+            del sys.modules[k]
+        sys.modules.update(saved)
+        for name in added:
+            sys.modules.pop(name, None)
+        if not had_nan:
+            try:
+                del _np.NaN
+            except AttributeError:
+                pass
+    return mod
+
+
+def rw_analysis():
+    """The reference's loihirw/rw_analysis.py (pure NumPy apart from its NxSDK star-import)."""
+    if "rw_analysis" not in _cache:
+        _cache["rw_analysis"] = _load_packaged("loihirw/rw_analysis.py", "_nrw_ref_rw_analysis")
+    return _cache["rw_analysis"]
+
+
+def rw_core():
+    """The reference's loihirw/rw_core.py (only get_probCircuitValues is NxSDK-free)."""
+    if "rw_core" not in _cache:
+        _cache["rw_core"] = _load_packaged("loihirw/rw_core.py", "_nrw_ref_rw_core")
+    return _cache["rw_core"]
+
+
+def density_rw():
+    """The reference's densityrw/DensityRW.py (load_transitions, build_test_graph)."""
+    if "density_rw" not in _cache:
+        _cache["density_rw"] = _load_packaged("densityrw/DensityRW.py", "_nrw_ref_density_rw")
+    return _cache["density_rw"]

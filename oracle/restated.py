@@ -176,7 +176,9 @@ def run_pc_counts(indptr, cols, cum, neuraltime, initial_walkers, meshSize,
     used = 0
     rowlen = np.diff(indptr)
     for t in range(1, neuraltime):
-        alive = nodes < meshSize                      # sink row is never stepped (:241)
+        # sink row is never stepped (:241); a row < meshSize WITHOUT entries makes the reference
+        # raise IndexError -- on such graphs (densityrw surface) walkers are absorbed instead
+        alive = (nodes < meshSize) & (rowlen[np.minimum(nodes, len(rowlen) - 1)] > 0)
         nodes_a, cnts_a = nodes[alive], cnts[alive]
         n = int(cnts_a.sum())
         if n == 0:

@@ -219,7 +219,11 @@ def test_dispatch_table_keeps_the_reference_modes():
         assert set(app.run_functions) == {"fugu", "loihi", "spinnaker", "pc"}
         assert app.run_functions["pc"] is app.run_pc
         with pytest.raises(NotImplementedError, match="-r pc"):
-            app.run_functions["loihi"](matrix_filename="m", neuraltime=1, initial_walkers=[[0, 1]], meshSize=1)
+            app.run_functions["spinnaker"](matrix_filename="m", neuraltime=1, initial_walkers=[[0, 1]], meshSize=1)
+        # 'fugu' / 'loihi' are the reference's adapters over this build's densityrw / loihirw surfaces
+        from nrw import dropin
+        assert app.run_functions["fugu"] is dropin.fugu_adapter
+        assert app.run_functions["loihi"] is dropin.loihi_adapter
 
 
 def test_pc_mode_fails_loudly_without_a_gpu(tmp_path, c1_csr):
