@@ -10,6 +10,9 @@
 #include "post.cuh"
 #include "walk_philox.cuh"
 #include "walk_replay.cuh"
+#include "walk_score.cuh"
+
+#include <cstdlib>
 
 using namespace nrw;
 
@@ -192,6 +195,7 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
     p.start_id_base = (const long long*)w->start_id_base;
     p.lo = w->walker_lo; p.hi = w->walker_hi;
     p.key = seed_to_key(w->seed); p.nt = w->nt;
+    for (int r = 0; r < 10; ++r) p.rk[r] = p.key + (uint32_t)r * PHILOX_W32;
     p.score = (long long*)w->score; p.score_sq = w->score_sq; p.tw = w->time_weight;
     p.cwpack = 0;
     for (int i = 0; i < 4; ++i) {
@@ -279,6 +283,24 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
     }
     NRW_WALK_VARIANTS(X)
 #undef X
+    // score-only walks on compact tables take the trimmed kernel (walk_score.cuh); the environment
+    // variable NRW_K1=general forces the general kernel (A/B measurements, parity tests of both)
+    if (tl == TL_SCORE && !w->score_sq && w->nt >= 2 && (tab == TAB_SMEM || tab == TAB_HYB)) {
+        const char* force = getenv("NRW_K1");
+        const bool general = force && strcmp(force, "general") == 0;
+        const bool idw = p.cwpack == 0x03020100u;
+        if (!general) {
+            // a lane's 32-bit step counter is flushed at every range fetch: keep range * nt < 2^32
+            while (p.range > 32 && p.range * (long long)w->nt >= (1ll << 32)) p.range = ((p.range / 2) / 32) * 32;
+#define Y(TAB, IDW)                                                            \
+    if (tab == TAB && idw == IDW) {                                            \
+        plan->fn = (const void*)walk_score_kernel<TAB, IDW>;                   \
+        plan->name = "walk_score<" #TAB "," #IDW ">";                          \
+    }
+            Y(TAB_SMEM, true) Y(TAB_SMEM, false) Y(TAB_HYB, true) Y(TAB_HYB, false)
+#undef Y
+        }
+    }
     if (!plan->fn)
         return fail(NRW_EINVAL, "nrw_walk_philox: tally combination %d is not built for table mode %d "
                     "(score=1 time_weight=2 hist_smem=4 hist_global=8 count_smem=16 count_global=32)",
@@ -383,7 +405,15 @@ extern "C" int nrw_fluence_scores_host(nrw_engine* e, int32_t n_rows, int32_t n_
     w.start_prefix = (const int64_t*)e->d_prefix;
     w.walker_lo = walker_lo; w.walker_hi = walker_hi; w.seed = seed; w.nt = nt;
     w.sampler = NRW_SAMPLER_ALIAS; w.score = (int64_t*)e->d_score;
-    for (int i = 0; i < 4; ++i) w.class_value[i] = class_value[i];
+    {   // weights of classes no row carries are free: if the used ones equal the class index, pass the
+        // identity vector so that the walk takes the IDW kernel (walk_score.cuh)
+        uint32_t max_cls = 0;
+        const uint32_t* ri = (const uint32_t*)rowinfo_host;
+        for (int32_t r = 0; r < n_rows; ++r) { const uint32_t c = ri[2 * r] >> 30; if (c > max_cls) max_cls = c; }
+        bool ident = true;
+        for (uint32_t c = 0; c <= max_cls; ++c) ident = ident && class_value[c] == (double)c;
+        for (int i = 0; i < 4; ++i) w.class_value[i] = ident ? (double)i : class_value[i];
+    }
     w.counters = e->d_counters;
     if ((rc = nrw_walk_philox(e, &t, &w, stream))) return rc;
     CUDA_TRY(cudaMemcpyAsync(score_host, e->d_score, (size_t)n_starts * 8, cudaMemcpyDeviceToHost, st));

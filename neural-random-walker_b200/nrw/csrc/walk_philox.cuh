@@ -36,6 +36,7 @@ struct WalkParams {
     int n_starts; const int32_t* start_nodes; const long long* start_prefix; const long long* start_id_base;
     long long lo, hi;
     uint32_t key; int nt;
+    uint32_t rk[10];                             // Philox round keys key + r * W32
     long long* score; double* score_sq;
     uint32_t cwpack; double cv[4]; const double* tw;
     unsigned long long* node_hist;
@@ -80,20 +81,14 @@ __device__ __forceinline__ uint32_t row_cls(const RowRegs<TAB>& r) {
     else return r.d & 3u;
 }
 
-template <int TAB, int TL>
-__global__ void __launch_bounds__(WALK_THREADS, 1)
-walk_philox_kernel(const __grid_constant__ WalkParams p) {
-    extern __shared__ __align__(16) unsigned char smem[];
-    uint64_t* bar = reinterpret_cast<uint64_t*>(smem);
-    uint2* rowinfo_s = reinterpret_cast<uint2*>(smem + p.sm_rowinfo);
-    uint2* alias_s = reinterpret_cast<uint2*>(smem + p.sm_alias);
-    uint32_t* hist_s = reinterpret_cast<uint32_t*>(smem + p.sm_hist);
-    uint32_t* cnt_s = reinterpret_cast<uint32_t*>(smem + p.sm_cnt);
-    const int tid = threadIdx.x, lane = tid & 31;
-
-    // ---- stage the tables: TMA bulk copies complete on one mbarrier ---------------------------
-    constexpr bool kStage = (TAB == TAB_SMEM || TAB == TAB_HYB);
-    if constexpr (kStage) {
+// Stage the de-duplicated alias patterns (and, for TAB_SMEM, the row descriptors) into shared
+// memory: thread 0 arms one mbarrier with the byte count and issues 1-D TMA bulk copies (SASS
+// UBLKCP) in <= 32 KB pieces; an odd entry count leaves one 8-byte tail outside the 16-byte
+// granules, copied by thread 32.  Callers wait with mbar_wait(bar, 0) + __syncthreads().
+template <int TAB>
+__device__ __forceinline__ void stage_tables_issue(const WalkParams& p, uint64_t* bar, uint2* rowinfo_s,
+                                                   uint2* alias_s, int tid) {
+    if constexpr (TAB == TAB_SMEM || TAB == TAB_HYB) {
         if (tid == 0) mbar_init(bar, 1);
         __syncthreads();
         const uint32_t alias_bytes = ((uint32_t)p.n_alias * 8u) & ~15u;
@@ -110,13 +105,29 @@ walk_philox_kernel(const __grid_constant__ WalkParams p) {
                                  reinterpret_cast<const unsigned char*>(p.rowinfo) + o,
                                  min(32768u, row_bytes - o), bar);
         }
-        if (tid == 32) {   // an odd entry count leaves one 8-byte tail outside the 16-byte granules
+        if (tid == 32) {
             if (p.n_alias & 1)
                 alias_s[p.n_alias - 1] = __ldg(reinterpret_cast<const uint2*>(p.alias) + p.n_alias - 1);
             if (TAB == TAB_SMEM && (p.n_rows & 1))
                 rowinfo_s[p.n_rows - 1] = __ldg(reinterpret_cast<const uint2*>(p.rowinfo) + p.n_rows - 1);
         }
     }
+}
+
+template <int TAB, int TL>
+__global__ void __launch_bounds__(WALK_THREADS, 1)
+walk_philox_kernel(const __grid_constant__ WalkParams p) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    uint64_t* bar = reinterpret_cast<uint64_t*>(smem);
+    uint2* rowinfo_s = reinterpret_cast<uint2*>(smem + p.sm_rowinfo);
+    uint2* alias_s = reinterpret_cast<uint2*>(smem + p.sm_alias);
+    uint32_t* hist_s = reinterpret_cast<uint32_t*>(smem + p.sm_hist);
+    uint32_t* cnt_s = reinterpret_cast<uint32_t*>(smem + p.sm_cnt);
+    const int tid = threadIdx.x, lane = tid & 31;
+
+    // ---- stage the tables: TMA bulk copies complete on one mbarrier ---------------------------
+    constexpr bool kStage = (TAB == TAB_SMEM || TAB == TAB_HYB);
+    stage_tables_issue<TAB>(p, bar, rowinfo_s, alias_s, tid);
     if constexpr (TL & TL_HIST_S)
         for (int i = tid; i < p.n_rows; i += WALK_THREADS) hist_s[i] = 0u;
     if constexpr (TL & TL_CNT_S)

@@ -1,0 +1,199 @@
+// walk_score.cuh -- K1s: the score-only fast path of the on-device walk (the fused fluence solve).
+//
+// Same semantics as walk_philox_kernel<TAB, TL_SCORE> (walk_philox.cuh) -- identical Philox streams,
+// alias draws, tallies and counters, checked bit for bit against the numpy port -- with a hot loop
+// trimmed for the resource that bounds it (issue slots and the half-rate integer ALU pipe, see
+// DESIGN.md section 3):
+//   * refill with ONE vote per iteration: dead lanes rank themselves with popc and take consecutive
+//     ids; everything rare (range exhausted, next start node, 2^32 carry of the stream id, walkers on
+//     absorbing starts) sits behind warp-uniform or [[unlikely]] branches;
+//   * the Philox round keys come from the kernel parameters (constant-bank operands), not from
+//     uniform-register arithmetic repeated every iteration;
+//   * the score is added unconditionally each step and the step t = nt-1 (outside the solution sum,
+//     fluence_mini_app.py:428) is taken back out on the rare end-of-time path; walker-steps are
+//     accumulated as lifetimes at death instead of once per step;
+//   * IDW: class weights equal to the class index turn the weight lookup into one LEA.HI.
+// Requires nt >= 2 (the planner sends nt = 1 to the general kernel).
+#pragma once
+#include "walk_philox.cuh"
+
+namespace nrw {
+
+template <int TAB>
+__device__ __forceinline__ uint2 load_row2(const WalkParams& p, const uint2* rowinfo_s, int k) {
+    if constexpr (TAB == TAB_SMEM) return rowinfo_s[k];
+    else return __ldg(reinterpret_cast<const uint2*>(p.rowinfo) + k);
+}
+
+// Philox2x32-10 with the ten round keys read from the kernel parameters (constant bank operands of
+// the LOP3s) instead of being re-derived from the key in uniform registers every iteration.
+__device__ __forceinline__ uint2 philox2x32_10_rk(uint32_t c0, uint32_t c1, const WalkParams& p) {
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        const uint32_t hi = __umulhi(PHILOX_M2x32, c0);
+        const uint32_t lo = PHILOX_M2x32 * c0;
+        c0 = hi ^ p.rk[r] ^ c1;
+        c1 = lo;
+    }
+    return make_uint2(c0, c1);
+}
+
+template <int TAB, bool IDW>
+__global__ void __launch_bounds__(WALK_THREADS, 1)
+walk_score_kernel(const __grid_constant__ WalkParams p) {
+    static_assert(TAB == TAB_SMEM || TAB == TAB_HYB, "compact alias tables only");
+    extern __shared__ __align__(16) unsigned char smem[];
+    uint64_t* bar = reinterpret_cast<uint64_t*>(smem);
+    const uint2* rowinfo_s = reinterpret_cast<const uint2*>(smem + p.sm_rowinfo);
+    const uint2* alias_s = reinterpret_cast<const uint2*>(smem + p.sm_alias);
+    const int tid = threadIdx.x, lane = tid & 31;
+    stage_tables_issue<TAB>(p, bar, reinterpret_cast<uint2*>(smem + p.sm_rowinfo),
+                            reinterpret_cast<uint2*>(smem + p.sm_alias), tid);
+    mbar_wait(bar, 0);
+    __syncthreads();
+
+    const int t_last = p.nt - 1;                 // last model step (fluence_mini_app.py:236); >= 1 here
+    const uint32_t lt_mask = lanemask_lt();
+
+    // ---- the lane's walker --------------------------------------------------------------------------
+    int t = -1;                                  // steps taken; -1 = no walker
+    uint32_t c0 = 0, chi = 0, ra = 0, rb = 0, x = 0;
+    // ---- the start the lane accumulates for (changes on the cold path only) -----------------------
+    int s = -1;
+    long long s_end = 0, sid_base = 0;
+    uint32_t s_end_off = 0, c0_base = 0, chi_base = 0;
+    int t_init = 0;
+    uint2 srow = make_uint2(0, 0);
+    long long acc = 0;
+    uint32_t nst = 0, nsurv = 0;                 // nst: < 2^32 between range fetches (range * nt bound)
+    unsigned long long nsteps = 0;
+    // ---- warp-uniform id range [rbase + cur, rbase + end) ------------------------------------------
+    long long rbase = 0;
+    uint32_t cur = 0, end = 0;
+    unsigned long long wwalk = 0;
+    bool exhausted = false;
+
+    auto flush_score = [&]() {
+        if (s >= 0 && acc != 0)
+            atomicAdd(reinterpret_cast<unsigned long long*>(p.score) + s, (unsigned long long)acc);
+        acc = 0;
+    };
+    auto rebase = [&]() {                        // after sid_base / rbase / s_end changed
+        const long long d = s_end - rbase;
+        s_end_off = d <= 0 ? 0u : (d > 0x7fffffffll ? 0x7fffffffu : (uint32_t)d);
+        c0_base = (uint32_t)sid_base;
+        chi_base = (uint32_t)((unsigned long long)sid_base >> 32) << 24;
+    };
+    // cold: the id at range offset `off` belongs to a later start than the lane's current one
+    auto next_start = [&](uint32_t off) {
+        const long long gnew = rbase + (long long)off;
+        flush_score();
+        long long s_lo = s_end;
+        bool found = false;
+        if (s >= 0 && s + 1 < p.n_starts) {
+            const long long e2 = __ldg(p.start_prefix + s + 2);
+            if (gnew < e2) { ++s; s_end = e2; found = true; }
+        }
+        if (!found) {
+            int lo_i = 0, hi_i = p.n_starts;
+            while (hi_i - lo_i > 1) {
+                const int mid = (lo_i + hi_i) >> 1;
+                if (__ldg(p.start_prefix + mid) <= gnew) lo_i = mid; else hi_i = mid;
+            }
+            s = lo_i;
+            s_lo = __ldg(p.start_prefix + s);
+            s_end = __ldg(p.start_prefix + s + 1);
+        }
+        srow = load_row2<TAB>(p, rowinfo_s, __ldg(p.start_nodes + s));
+        sid_base = rbase + (p.start_id_base ? (__ldg(p.start_id_base + s) - s_lo) : 0ll);
+        rebase();
+        t_init = ((srow.x & 0x3ff00000u) == 0u) ? -1 : 0;      // started on the sink: an exit, no step
+    };
+    auto take = [&](uint32_t off) {
+        if (off >= s_end_off) [[unlikely]] next_start(off);
+        c0 = c0_base + off;
+        chi = chi_base + ((c0 < c0_base) ? (1u << 24) : 0u);   // carry into the id's bits 32..39
+        ra = srow.x; rb = srow.y;
+        t = t_init; x = 0;
+    };
+
+    while (true) {
+        // ---- refill: one vote ranks the dead lanes; they take consecutive ids of the warp's range --
+        const bool dead = t < 0;
+        const unsigned need = __ballot_sync(NRW_FULL_MASK, dead);
+        const uint32_t off = cur + (uint32_t)__popc(need & lt_mask);
+        const uint32_t ncur = cur + (uint32_t)__popc(need);
+        if (ncur <= end) {
+            cur = ncur;
+            if (dead) take(off);
+        } else {
+            // cold (once per id range): serve what the range still holds, then fetch the next one;
+            // lanes left without an id idle for this one iteration
+            if (dead && off < end) take(off);
+            cur = end;
+            if (!exhausted) {
+                nsteps += nst; nst = 0;
+                long long a = 0;
+                if (lane == 0) a = (long long)atomicAdd(p.work_next, (unsigned long long)p.range);
+                a = __shfl_sync(NRW_FULL_MASK, a, 0);
+                const long long nb = p.lo + a;
+                if (nb >= p.hi) exhausted = true;
+                else {
+                    cur = 0;
+                    end = (uint32_t)min(p.range, p.hi - nb);
+                    wwalk += end;
+                    sid_base += nb - rbase;
+                    rbase = nb;
+                    rebase();
+                }
+            }
+            if (exhausted && !__any_sync(NRW_FULL_MASK, t >= 0)) break;
+        }
+
+        // refilled and surviving lanes step together (without this the compiler sends the two groups
+        // through the step code separately)
+        __syncwarp();
+
+        // ---- one model step (fluence_mini_app.py:243-245 + the fused :428-434) -----------------------
+        if (t >= 0) {
+            const int tn = t + 1;
+            const uint2 r = philox2x32_10_rk(c0, chi | (uint32_t)tn, p);
+            const uint32_t n = (ra >> 20) & 0x3ffu, aoff = ra & 0xfffffu;
+            const uint2 e = alias_s[aoff + __umulhi(r.x, n)];
+            const int knew = (int)(rb + ((r.y <= e.x) ? (e.y & 0xffffu) : (e.y >> 16)));
+            const uint2 row = load_row2<TAB>(p, rowinfo_s, knew);
+            ra = row.x; rb = row.y;
+            const uint32_t wgt = IDW ? (row.x >> 30) : ((p.cwpack >> ((row.x >> 27) & 0x18u)) & 0xffu);
+            x += wgt;
+            t = tn;
+            const bool absorbed = (row.x & 0x3ff00000u) == 0u;
+            if (absorbed || tn >= t_last) {
+                if (tn >= t_last) [[unlikely]] {  // step nt-1 is outside the sum (:428, Q3)
+                    x -= wgt;
+                    if (!absorbed) ++nsurv;
+                }
+                acc += (long long)x;
+                nst += (uint32_t)tn;
+                t = -1;
+            }
+        }
+    }
+
+    // ---- epilogue ------------------------------------------------------------------------------------
+    flush_score();
+    unsigned long long v0 = nsteps + nst;
+    uint32_t v2 = nsurv;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        v0 += __shfl_xor_sync(NRW_FULL_MASK, v0, o);
+        v2 += __shfl_xor_sync(NRW_FULL_MASK, v2, o);
+    }
+    if (lane == 0 && p.counters) {
+        if (v0) atomicAdd(p.counters + 0, v0);
+        if (wwalk - v2) atomicAdd(p.counters + 1, wwalk - v2);          // exits = walkers - survivors
+        if (v2) atomicAdd(p.counters + 2, (unsigned long long)v2);
+        if (wwalk) atomicAdd(p.counters + 4, wwalk);
+    }
+}
+
+}  // namespace nrw

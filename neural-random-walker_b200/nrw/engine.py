@@ -101,6 +101,17 @@ def load_library():
     return lib
 
 
+def identity_weights_if_equivalent(cv, max_class):
+    """Weights of classes no row carries cannot change any tally; when the weights of the classes
+    in use equal the class index, hand the kernel the full identity vector [0, 1, 2, 3] -- it then
+    reads the weight straight out of the row descriptor (the IDW variants of walk_score.cuh)."""
+    cv = np.asarray(cv, dtype=np.float64).copy()
+    k = int(max_class) + 1
+    if np.array_equal(cv[:k], np.arange(k, dtype=np.float64)):
+        cv[:] = np.arange(4, dtype=np.float64)
+    return cv
+
+
 def _ptr(t):
     return None if t is None else C.c_void_p(t.data_ptr())
 
@@ -118,6 +129,7 @@ class DeviceTables:
     rowinfo: object
     alias: object
     struct: _Tables
+    max_class: int = 0          # largest source class any row carries (weights of unused classes are free)
 
     @property
     def n_rows(self):
@@ -254,7 +266,8 @@ class Engine:
             alias_t = self._dev(at.alias, np.uint32)
             st.alias_layout, st.n_alias = ALIAS_LAYOUT[at.layout], at.n_alias
             st.rowinfo, st.alias = _ptr(rowinfo), _ptr(alias_t)
-        return DeviceTables(csr, indptr, cols, vals, cum, nc, at, rowinfo, alias_t, st)
+        max_class = 0 if node_class is None else int(np.asarray(node_class).max(initial=0))
+        return DeviceTables(csr, indptr, cols, vals, cum, nc, at, rowinfo, alias_t, st, max_class)
 
     # ------------------------------------------------------------------ K1
     def _walk_struct(self, tables, start_nodes, start_counts, nt, seed, walker_range, sampler,
@@ -290,7 +303,8 @@ class Engine:
         w.nt, w.sampler = int(nt), SAMPLER[sampler]
         res = WalkResult(counters=torch.zeros(NRW_N_COUNTERS, dtype=torch.int64, device=self.device))
         w.counters = _ptr(res.counters)
-        cv = np.zeros(4) if class_value is None else np.asarray(class_value, dtype=np.float64)
+        cv = np.zeros(4) if class_value is None else np.asarray(class_value, dtype=np.float64).copy()
+        cv = identity_weights_if_equivalent(cv, tables.max_class)
         w.class_value = (C.c_double * 4)(*cv.tolist())
         if score:
             res.score = torch.zeros(n_starts, dtype=torch.int64, device=self.device)

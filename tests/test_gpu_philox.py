@@ -283,7 +283,7 @@ def test_errors(engine, c1_csr, tmp_path):
         a.update(matrix_filename=str(tmp_path / "m.csv"), results_filename=str(tmp_path / "r.csv"))
         app.run(a)
     with pytest.raises(NotImplementedError):
-        app.run_functions["fugu"](matrix_filename="x", neuraltime=3, initial_walkers=[[0, 1]], meshSize=900)
+        app.run_functions["spinnaker"](matrix_filename="x", neuraltime=3, initial_walkers=[[0, 1]], meshSize=900)
     tabs = engine.upload(c1_csr)
     with pytest.raises(IndexError):
         engine.walk(tabs, [901], 1, 10, 0, node_hist=True)
@@ -291,3 +291,87 @@ def test_errors(engine, c1_csr, tmp_path):
         engine.walk(tabs, [0], 1, 10, 0)                       # no tally requested
     with pytest.raises(NrwError):
         engine.walk(tabs, [0], 1, 1 << 25, 0, node_hist=True)  # nt beyond the counter's 24 bits
+
+
+# ---------------------------------------------------------------- K1s: the score-only fast path
+@pytest.fixture
+def k1_env(monkeypatch):
+    def set_variant(variant):
+        monkeypatch.delenv("NRW_K1", raising=False)
+        if variant == "general":
+            monkeypatch.setenv("NRW_K1", "general")
+    return set_variant
+
+
+@pytest.mark.parametrize("variant", ["fast", "general"])
+def test_score_fast_path_bit_exact_all_variants(engine, c1_csr, k1_env, variant):
+    """walk_score_kernel and the general kernel produce the same integers as the numpy port:
+    identity and packed class weights, ragged starts with the sink and empty starts in the list,
+    sub-ranges, sharded stream ids (incl. a 2^32 carry inside a start), nt edge cases."""
+    from nrw import mesh
+    from oracle import philox_port
+    k1_env(variant)
+    _, nc1, _ = _classes(c1_csr, mesh.source_default)                    # classes {0, 1}
+    nc3 = (np.arange(c1_csr.n_rows) % 4).astype(np.uint8)                # classes {0, 1, 2, 3}
+    nc3[900] = 2                                                         # a weighted sink
+    want = {"fast": "walk_score<TAB_SMEM", "general": "walk_philox<"}[variant]
+    starts = np.array([435, 0, 900, 14, 14, 899, 450, 16, 464])
+    counts = np.array([3000, 0, 17, 1, 333, 64, 5, 2500, 1200])
+    total = int(counts.sum())
+    carry = np.arange(9) * 2 ** 33 + (2 ** 32 - 1500)                    # ids cross a multiple of 2^32
+    for nc, cv, idw in ((nc1, [0, 1, 0, 0], True), (nc1, [0, 7, 0, 0], False), (nc3, [0, 1, 2, 3], True),
+                        (nc3, [5, 0, 255, 1], False)):
+        tabs = engine.upload(c1_csr, node_class=nc)
+        for nt, rng_, idb in ((64, None, None), (64, (2999, 3400), None), (3, None, None), (2, None, None),
+                              (1, None, None), (40, None, carry), (64, (total - 1, total), None)):
+            res = engine.walk(tabs, starts, counts, nt, 5, score=True, class_value=cv, walker_range=rng_,
+                              start_id_base=idb)
+            if nt >= 2:
+                assert want in res.kernel, res.kernel
+                if variant == "fast":
+                    assert res.kernel.endswith("true>" if idw else "false>"), res.kernel
+            else:
+                assert "walk_philox<" in res.kernel                      # nt = 1: no step at all
+            port = philox_port.walk_port(c1_csr, starts, counts, nt, 5, alias=tabs.alias_host, class_value=cv,
+                                         walker_range=rng_, start_id_base=idb)
+            _cmp(res, port, hist=False)
+    # a long uniform start list: many range fetches and start changes per warp
+    tabs = engine.upload(c1_csr, node_class=nc1)
+    res = engine.walk(tabs, np.arange(900), 777, 64, 6, score=True, class_value=[0, 1, 0, 0])
+    port = philox_port.walk_port(c1_csr, np.arange(900), 777, 64, 6, alias=tabs.alias_host,
+                                 class_value=[0, 1, 0, 0])
+    _cmp(res, port, hist=False)
+
+
+def test_score_fast_path_hybrid_tables_and_survivors(engine, k1_env):
+    """Row descriptors in L2 (TAB_HYB) + walkers that outlive nt (survivors; the step t = nt-1 is
+    outside the solution sum, fluence_mini_app.py:428)."""
+    from nrw import mesh
+    from oracle import philox_port
+    k1_env("fast")
+    csr = mesh.build_fluence_csr(0.001, 1.0 / 31.0, 200, 0.15, 1)
+    _, nc, _ = _classes(csr, mesh.source_default)
+    tabs = engine.upload(csr, node_class=nc)
+    starts = np.arange(0, csr.n_live, 97)
+    for nt in (400, 9):                                  # nt = 9: most walkers survive
+        res = engine.walk(tabs, starts, 48, nt, 6, score=True, class_value=[0, 1, 0, 0])
+        assert "walk_score<TAB_HYB" in res.kernel, res.kernel
+        port = philox_port.walk_port(csr, starts, 48, nt, 6, alias=tabs.alias_host, class_value=[0, 1, 0, 0])
+        _cmp(res, port, hist=False)
+    assert port["counters"]["survivors"] > 0
+
+
+def test_score_fast_path_equals_general_kernel_at_full_size(engine, k1_env):
+    """C5 mesh, 1e7 walkers: the trimmed kernel and the general kernel agree on every score."""
+    from nrw import mesh
+    csr = mesh.build_fluence_csr(0.01, 0.02, 200, 0.15, 1)
+    _, nc, _ = _classes(csr, mesh.source_default)
+    tabs = engine.upload(csr, node_class=nc)
+    out = {}
+    for variant in ("fast", "general"):
+        k1_env(variant)
+        r = engine.walk(tabs, np.arange(10000), 1000, 30000, 3, score=True, class_value=[0, 1, 0, 0])
+        out[variant] = (r.score.cpu().numpy(), r.counters_dict(), r.kernel)
+    assert "walk_score<" in out["fast"][2] and "walk_philox<" in out["general"][2]
+    assert np.array_equal(out["fast"][0], out["general"][0])
+    assert out["fast"][1] == out["general"][1]
