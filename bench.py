@@ -190,7 +190,7 @@ def run_reference_arm(args):
             "cpu_baseline": dict(value=value, unit=METRIC, cores=1, kind="port", sample=sample),
             "e2e": {"value": value, "unit": METRIC, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0, "wall_s": time.perf_counter() - t_all}
-    print(json.dumps(line), flush=True)
+    _emit(json.dumps(line))
 
 
 def workload_config(args):
@@ -367,7 +367,7 @@ def run_ours(args):
     elif rank == 0:
         line["cpu_baseline"] = None
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        _emit(json.dumps(line))
     if world > 1:
         tdist.barrier()
         tdist.destroy_process_group()
@@ -407,8 +407,29 @@ def c2_leg(eng):
     return out
 
 
+def _protect_stdout():
+    """The contract is ONE JSON line on stdout.  Libraries write there too (NCCL prints its version
+    banner to stdout on the first collective), so file descriptor 1 is pointed at stderr for the
+    duration of the run and the JSON line goes to the saved descriptor."""
+    sys.stdout.flush()
+    saved = os.dup(1)
+    os.dup2(2, 1)
+    out = os.fdopen(saved, "w")
+
+    def emit(line):
+        out.write(line + "\n")
+        out.flush()
+    return emit
+
+
+_emit = print
+
+
 def main():
+    global _emit
     args = parse_args()
+    os.environ.setdefault("NCCL_DEBUG", "WARN")
+    _emit = _protect_stdout()
     if args.impl == "reference":
         run_reference_arm(args)
     else:
