@@ -53,7 +53,7 @@ def parse_args():
 # helpers
 # ------------------------------------------------------------------------------------------------
 class ClockSampler:
-    """SM clock + throttle reasons during the timed region (NVML, 20 ms period)."""
+    """SM clock + throttle reasons during the timed region (NVML, 5 ms period)."""
     REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown",
                0x4: "sw_power_cap", 0x80: "hw_power_brake", 0x2: "applications_clocks_setting"}
 
@@ -80,7 +80,7 @@ class ClockSampler:
                         self.reasons.add(name)
             except Exception:
                 pass
-            self._stop.wait(0.02)
+            self._stop.wait(0.005)
 
     def __enter__(self):
         if self.nv is not None:
@@ -283,6 +283,33 @@ def run_ours(args):
     torch.cuda.synchronize()
     kernel_ms = float(np.mean([a.elapsed_time(b) for a, b in kev]))
 
+    # ---- ablation (kernel alone, same launch descriptor): draws on deterministic rows too / general kernel
+    ablation = {}
+    if rank == 0 and not args.no_extras:
+        for tag, env in (("always_draw_NRW_DET=0", {"NRW_DET": "0"}), ("general_kernel_NRW_K1=general", {"NRW_K1": "general"})):
+            old_env = {k: os.environ.get(k) for k in env}
+            os.environ.update(env)
+            try:
+                for _ in range(3):
+                    launch()
+                ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(10)]
+                for a, b in ev:
+                    flush.fill_(1)
+                    launch.zero()
+                    a.record()
+                    launch.launch_kernel()
+                    b.record()
+                torch.cuda.synchronize()
+                ms_ab = float(np.mean([a.elapsed_time(b) for a, b in ev]))
+                assert int(res.counters.cpu()[0].item()) == steps_per_launch      # same walk, same count
+                ablation[tag] = {"kernel_ms": ms_ab, "walker_steps_per_s": steps_per_launch / (ms_ab * 1e-3)}
+            finally:
+                for k, v in old_env.items():
+                    if v is None:
+                        os.environ.pop(k, None)
+                    else:
+                        os.environ[k] = v
+
     line = None
     if rank == 0:
         # occupancy (walker-steps taken FROM each node) for the algorithmic-bytes figure: one untimed
@@ -295,27 +322,38 @@ def run_ours(args):
         b_step = algorithmic_bytes_per_step(csr, steps_from)
         peak, peak_src = measured_peak()
         achieved = steps_per_launch * b_step / (kernel_ms * 1e-3) / 1e9
-        traffic = None
+        traffic, ncu_facts = None, {}
         tp = os.path.join(ROOT, "profiles", "walk_traffic.json")
         if os.path.isfile(tp):
             try:
-                traffic = json.load(open(tp)).get("dram_bytes_per_launch")
+                ncu_facts = json.load(open(tp))
+                traffic = ncu_facts.get("dram_bytes_per_launch")
             except Exception:
                 traffic = None
+        lens = csr.row_lengths()[:n_nodes]
+        det_frac = float(steps_from[lens == 1].sum() / max(steps_from.sum(), 1.0))
         roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                     "frac": achieved / peak, "traffic": traffic, "kernel": res.kernel,
                     "kernel_ms": kernel_ms, "walker_steps_per_launch": steps_per_launch,
                     "algorithmic_bytes_per_walker_step": b_step, "peak_source": peak_src,
+                    "binding_resource": {"what": "SM issue slots (integer ALU + IMAD pipes), not memory",
+                                         "issue_slot_utilisation_ncu": ncu_facts.get("issue_active_pct"),
+                                         "warp_instructions_per_walker_step_ncu": ncu_facts.get("warp_inst_per_32_walker_steps"),
+                                         "source": ncu_facts.get("source")},
+                    "deterministic_step_fraction": det_frac,
                     "note": "algorithmic bytes are the reference algorithm's (SURVEY 8d: searchsorted "
-                            "probes on fp64 rows); the kernel serves them from shared memory, so HBM "
-                            "is not the binding resource -- see DESIGN.md for issue-slot accounting"}
+                            "probes on fp64 rows); the kernel serves them from shared memory and keeps "
+                            "walker state in registers, so HBM is not the binding resource and frac > 1 "
+                            "-- DESIGN.md section 3 gives the issue-slot accounting.  Steps from rows with "
+                            "a single absorbing successor (deterministic_step_fraction) are taken without "
+                            "computing a draw; results are bit-identical to always drawing (ablation)."}
         line = {"metric": METRIC, "value": value, "unit": METRIC, "n_gpus": world, "steps": args.steps,
                 "warmup": max(args.warmup, 3), "ms_per_step": total_ms / args.steps,
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32/f64",
                 "data": "synthetic", "config": workload_config(args), "roofline": roofline,
                 "walker_steps_per_step": job_steps, "walkers_per_step": n_nodes * Mg * world,
                 "gpu_launches": args.steps, "wall_s_timed_region": t_wall,
-                "launch_geometry": list(res.launch_geometry)}
+                "launch_geometry": list(res.launch_geometry), "ablation_kernel_only": ablation or None}
 
     # ---- e2e: the C-ABI host entry with HOST buffers, H2D + kernel + D2H inside the timed region --
     at = tabs.alias_host

@@ -44,10 +44,14 @@ typedef struct nrw_engine nrw_engine;   /* opaque handle: one per (process, devi
 /* ---- table layouts -------------------------------------------------------------- */
 /* alias_layout values */
 #define NRW_ALIAS_NONE    0
-#define NRW_ALIAS_COMPACT 1   /* rowinfo 8 B/row, alias 8 B/entry (fits shared memory)   */
+#define NRW_ALIAS_COMPACT 1   /* rowinfo 8 B/row, alias 8 B/entry, <= 2^15 entries (shared memory) */
 #define NRW_ALIAS_WIDE    2   /* rowinfo 16 B/row, alias 16 B/entry (any graph, global)  */
 
-/* COMPACT rowinfo  (uint32 w0, w1):  w0 = off[0:20) | n[20:30) | cls[30:32),  w1 = base
+/* COMPACT rowinfo  (uint32 w0, w1):  w0 = off[0:15) | n[15:25) | detcls[25:27) | detabs[27] | term[28] | cls[30:32),
+ *                  w1 = base.  detabs = 1: the row has ONE successor and it is absorbing (an exit row
+ *                  of fluence_mini_app.py:355-357); detcls = source class of that successor;
+ *                  term = (n == 0) | detabs.  The
+ *                  score kernel steps such rows without a draw (the draw cannot change the outcome).
  *         alias    (uint32 thresh, ab): target = base + ((r1 <= thresh) ? ab & 0xffff : ab >> 16)
  * WIDE    rowinfo  (uint32 off, n, base, cls)
  *         alias    (uint32 thresh, a, b, 0): target = base + ((r1 <= thresh) ? a : b)

@@ -39,6 +39,19 @@ __host__ __device__ __forceinline__ uint32_t seed_to_key(uint64_t seed) {
     return (uint32_t)(z ^ (z >> 32));
 }
 
+// ---- COMPACT row descriptor word 0 (include/nrw.h): off[0:15) | n[15:25) | detcls[25:27) | detabs[27] |
+//      term[28] | spare[29] | cls[30:32).  detabs marks a row whose single successor is absorbing; detcls
+//      is that successor's source class; term = (n == 0) | detabs: a walker landing here ends in this
+//      iteration (tables.py::build_alias).
+constexpr uint32_t ROW_OFF_MASK = 0x00007fffu;
+constexpr uint32_t ROW_N_MASK   = 0x01ff8000u;
+constexpr uint32_t ROW_DETABS   = 0x08000000u;
+constexpr uint32_t ROW_TERM     = 0x10000000u;
+__host__ __device__ __forceinline__ uint32_t row_off(uint32_t w0) { return w0 & ROW_OFF_MASK; }
+__host__ __device__ __forceinline__ uint32_t row_len(uint32_t w0) { return (w0 >> 15) & 0x3ffu; }
+__host__ __device__ __forceinline__ uint32_t row_detcls(uint32_t w0) { return (w0 >> 25) & 3u; }
+__host__ __device__ __forceinline__ uint32_t row_class(uint32_t w0) { return w0 >> 30; }
+
 // numpy legacy random_sample(): (a >> 5, b >> 6) -> 53-bit double in [0, 1).
 __device__ __forceinline__ double u53(uint32_t a, uint32_t b) {
     return ((double)(a >> 5) * 67108864.0 + (double)(b >> 6)) * (1.0 / 9007199254740992.0);

@@ -225,8 +225,8 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
         if (t->alias_layout == NRW_ALIAS_WIDE) {
             tab = TAB_GLB;
         } else if (t->alias_layout == NRW_ALIAS_COMPACT) {
-            if (t->n_alias > (1 << 20))
-                return fail(NRW_EINVAL, "nrw_walk_philox: compact layout holds < 2^20 alias entries");
+            if (t->n_alias > (1 << 15))
+                return fail(NRW_EINVAL, "nrw_walk_philox: compact layout holds <= 2^15 alias entries");
             const int ab = align16(t->n_alias * 8), rb = align16(t->n_rows * 8);
             if (16 + ab + rb <= e->max_smem) tab = TAB_SMEM;
             else if (16 + ab <= e->max_smem) tab = TAB_HYB;
@@ -289,15 +289,18 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
         const char* force = getenv("NRW_K1");
         const bool general = force && strcmp(force, "general") == 0;
         const bool idw = p.cwpack == 0x03020100u;
+        const char* det_env = getenv("NRW_DET");             // NRW_DET=0: draw on deterministic rows too
+        const bool det = !(det_env && strcmp(det_env, "0") == 0);
         if (!general) {
             // a lane's 32-bit step counter is flushed at every range fetch: keep range * nt < 2^32
             while (p.range > 32 && p.range * (long long)w->nt >= (1ll << 32)) p.range = ((p.range / 2) / 32) * 32;
-#define Y(TAB, IDW)                                                            \
-    if (tab == TAB && idw == IDW) {                                            \
-        plan->fn = (const void*)walk_score_kernel<TAB, IDW>;                   \
-        plan->name = "walk_score<" #TAB "," #IDW ">";                          \
+#define Y(TAB, IDW, DET)                                                       \
+    if (tab == TAB && idw == IDW && det == DET) {                              \
+        plan->fn = (const void*)walk_score_kernel<TAB, IDW, DET>;              \
+        plan->name = "walk_score<" #TAB "," #IDW "," #DET ">";                 \
     }
-            Y(TAB_SMEM, true) Y(TAB_SMEM, false) Y(TAB_HYB, true) Y(TAB_HYB, false)
+            Y(TAB_SMEM, true, true) Y(TAB_SMEM, false, true) Y(TAB_HYB, true, true) Y(TAB_HYB, false, true)
+            Y(TAB_SMEM, true, false) Y(TAB_SMEM, false, false) Y(TAB_HYB, true, false) Y(TAB_HYB, false, false)
 #undef Y
         }
     }

@@ -72,12 +72,12 @@ __device__ __forceinline__ RowRegs<TAB> load_row(const WalkParams& p, const uint
 }
 template <int TAB>
 __device__ __forceinline__ uint32_t row_n(const RowRegs<TAB>& r) {
-    if constexpr (TAB == TAB_SMEM || TAB == TAB_HYB) return (r.a >> 20) & 0x3ffu;
+    if constexpr (TAB == TAB_SMEM || TAB == TAB_HYB) return row_len(r.a);
     else return r.b;
 }
 template <int TAB>
 __device__ __forceinline__ uint32_t row_cls(const RowRegs<TAB>& r) {
-    if constexpr (TAB == TAB_SMEM || TAB == TAB_HYB) return r.a >> 30;
+    if constexpr (TAB == TAB_SMEM || TAB == TAB_HYB) return row_class(r.a);
     else return r.d & 3u;
 }
 
@@ -250,7 +250,7 @@ walk_philox_kernel(const __grid_constant__ WalkParams p) {
                 const uint4 e = __ldg(reinterpret_cast<const uint4*>(p.alias) + row.a + slot);
                 knew = (int)(row.c + ((r.y <= e.x) ? e.y : e.z));
             } else {
-                const uint32_t n = (row.a >> 20) & 0x3ffu, off = row.a & 0xfffffu;
+                const uint32_t n = row_len(row.a), off = row_off(row.a);
                 const uint32_t slot = __umulhi(r.x, n);
                 const uint2 e = alias_s[off + slot];
                 knew = (int)(row.b + ((r.y <= e.x) ? (e.y & 0xffffu) : (e.y >> 16)));

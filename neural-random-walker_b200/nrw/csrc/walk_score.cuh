@@ -12,7 +12,13 @@
 //   * the score is added unconditionally each step and the step t = nt-1 (outside the solution sum,
 //     fluence_mini_app.py:428) is taken back out on the rare end-of-time path; walker-steps are
 //     accumulated as lifetimes at death instead of once per step;
-//   * IDW: class weights equal to the class index turn the weight lookup into one LEA.HI.
+//   * IDW: class weights equal to the class index turn the weight lookup into one LEA.HI;
+//   * DET: a row whose single successor is absorbing (every exit row of the fluence mesh: 45 % of
+//     all walker-steps) is stepped without computing a draw -- slot 0 with threshold 2^32-1 is taken
+//     whatever the draw is, so tallies and counters stay bit-identical to the always-draw port.  A
+//     walker landing on such a row takes its exit step in the same iteration; walkers STARTING on
+//     one are accounted for by the refill (one step, one tally, exit) and never enter the step phase,
+//     so warps inside such a start node skip the step phase altogether.  NRW_DET=0 disables it.
 // Requires nt >= 2 (the planner sends nt = 1 to the general kernel).
 #pragma once
 #include "walk_philox.cuh"
@@ -38,7 +44,7 @@ __device__ __forceinline__ uint2 philox2x32_10_rk(uint32_t c0, uint32_t c1, cons
     return make_uint2(c0, c1);
 }
 
-template <int TAB, bool IDW>
+template <int TAB, bool IDW, bool DET>
 __global__ void __launch_bounds__(WALK_THREADS, 1)
 walk_score_kernel(const __grid_constant__ WalkParams p) {
     static_assert(TAB == TAB_SMEM || TAB == TAB_HYB, "compact alias tables only");
@@ -63,6 +69,7 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
     long long s_end = 0, sid_base = 0;
     uint32_t s_end_off = 0, c0_base = 0, chi_base = 0;
     int t_init = 0;
+    uint32_t det_w = 0, det_n = 0;               // DET: walkers of a deterministic-exit start
     uint2 srow = make_uint2(0, 0);
     long long acc = 0;
     uint32_t nst = 0, nsurv = 0;                 // nst: < 2^32 between range fetches (range * nt bound)
@@ -73,6 +80,9 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
     unsigned long long wwalk = 0;
     bool exhausted = false;
 
+    auto weight_of = [&](uint32_t cls) -> uint32_t {
+        return IDW ? cls : ((p.cwpack >> (cls * 8u)) & 0xffu);
+    };
     auto flush_score = [&]() {
         if (s >= 0 && acc != 0)
             atomicAdd(reinterpret_cast<unsigned long long*>(p.score) + s, (unsigned long long)acc);
@@ -107,7 +117,15 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
         srow = load_row2<TAB>(p, rowinfo_s, __ldg(p.start_nodes + s));
         sid_base = rbase + (p.start_id_base ? (__ldg(p.start_id_base + s) - s_lo) : 0ll);
         rebase();
-        t_init = ((srow.x & 0x3ff00000u) == 0u) ? -1 : 0;      // started on the sink: an exit, no step
+        t_init = ((srow.x & ROW_N_MASK) == 0u) ? -1 : 0;       // started on the sink: an exit, no step
+        if constexpr (DET) {
+            // a start whose single successor is absorbing: every walker takes that one step (t = 1)
+            // and exits; no draw can change it, so the take accounts for it and the lane stays free
+            const bool det = (srow.x & ROW_DETABS) != 0u;
+            det_n = det ? 1u : 0u;
+            det_w = (det && t_last >= 2) ? weight_of(row_detcls(srow.x)) : 0u;   // t = nt-1 is outside the sum
+            if (det) t_init = -1;
+        }
     };
     auto take = [&](uint32_t off) {
         if (off >= s_end_off) [[unlikely]] next_start(off);
@@ -115,6 +133,7 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
         chi = chi_base + ((c0 < c0_base) ? (1u << 24) : 0u);   // carry into the id's bits 32..39
         ra = srow.x; rb = srow.y;
         t = t_init; x = 0;
+        if constexpr (DET) { acc += (long long)det_w; nst += det_n; }
     };
 
     while (true) {
@@ -158,22 +177,36 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
         if (t >= 0) {
             const int tn = t + 1;
             const uint2 r = philox2x32_10_rk(c0, chi | (uint32_t)tn, p);
-            const uint32_t n = (ra >> 20) & 0x3ffu, aoff = ra & 0xfffffu;
+            const uint32_t n = row_len(ra), aoff = row_off(ra);
             const uint2 e = alias_s[aoff + __umulhi(r.x, n)];
             const int knew = (int)(rb + ((r.y <= e.x) ? (e.y & 0xffffu) : (e.y >> 16)));
             const uint2 row = load_row2<TAB>(p, rowinfo_s, knew);
             ra = row.x; rb = row.y;
-            const uint32_t wgt = IDW ? (row.x >> 30) : ((p.cwpack >> ((row.x >> 27) & 0x18u)) & 0xffu);
+            uint32_t wgt = IDW ? (row.x >> 30) : ((p.cwpack >> ((row.x >> 27) & 0x18u)) & 0xffu);
             x += wgt;
             t = tn;
-            const bool absorbed = (row.x & 0x3ff00000u) == 0u;
-            if (absorbed || tn >= t_last) {
-                if (tn >= t_last) [[unlikely]] {  // step nt-1 is outside the sum (:428, Q3)
+            // the walk ends here when the row is absorbing, when (DET) its single successor is, or at
+            // the last model step
+            const bool terminal = (row.x & (DET ? ROW_TERM : ROW_N_MASK)) == (DET ? ROW_TERM : 0u);
+            if (terminal || tn >= t_last) {
+                int tl = tn;
+                bool absorbed = (row.x & ROW_N_MASK) == 0u;
+                if constexpr (DET) {
+                    // single absorbing successor (fluence exit rows, fluence_mini_app.py:355-357): take
+                    // that step now -- no draw could change it
+                    if (!absorbed && tn < t_last) {
+                        wgt = weight_of(row_detcls(row.x));
+                        x += wgt;
+                        tl = tn + 1;
+                        absorbed = true;
+                    }
+                }
+                if (tl >= t_last) [[unlikely]] {  // step nt-1 is outside the sum (:428, Q3)
                     x -= wgt;
                     if (!absorbed) ++nsurv;
                 }
                 acc += (long long)x;
-                nst += (uint32_t)tn;
+                nst += (uint32_t)tl;
                 t = -1;
             }
         }

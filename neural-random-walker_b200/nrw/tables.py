@@ -25,7 +25,8 @@ from .mesh import TransitionCSR
 
 COMPACT_MAX_N = 1023
 COMPACT_MAX_REL = 65535
-COMPACT_MAX_ENTRIES = 1 << 20
+COMPACT_MAX_ENTRIES = 1 << 15          # offsets are 15 bits: what one SM's shared memory can hold anyway
+ROW_N_SHIFT, ROW_DETCLS_SHIFT, ROW_DETABS_BIT, ROW_TERM_BIT, ROW_CLS_SHIFT = 15, 25, 27, 28, 30
 
 
 def row_cum(csr: TransitionCSR) -> np.ndarray:
@@ -162,7 +163,14 @@ def build_alias(csr: TransitionCSR, node_class: np.ndarray | None = None,
     row_n[csr.n_live:] = 0                                     # rows >= n_live are never stepped
     row_base = base.astype(np.uint32)
     if layout == "compact":
-        w0 = row_off | (row_n << np.uint32(20)) | (node_class << np.uint32(30))
+        # deterministic exits: one successor, and that successor is never stepped (absorbing)
+        first = csr.cols[np.minimum(csr.indptr[:-1], max(csr.nnz - 1, 0))].astype(np.int64) if csr.nnz else np.zeros(n, np.int64)
+        detabs = (row_n == 1) & (row_n[first] == 0)
+        detcls = np.where(detabs, node_class[first], 0).astype(np.uint32)
+        w0 = (row_off | (row_n << np.uint32(ROW_N_SHIFT)) | (detcls << np.uint32(ROW_DETCLS_SHIFT))
+              | (detabs.astype(np.uint32) << np.uint32(ROW_DETABS_BIT))
+              | ((detabs | (row_n == 0)).astype(np.uint32) << np.uint32(ROW_TERM_BIT))
+              | (node_class << np.uint32(ROW_CLS_SHIFT)))
         rowinfo = np.stack([w0, row_base], axis=1).astype(np.uint32)
         ab = (a_all.astype(np.uint32) & np.uint32(0xFFFF)) | (b_all.astype(np.uint32) << np.uint32(16))
         alias = np.stack([th_all, ab], axis=1).astype(np.uint32)
@@ -183,7 +191,7 @@ def alias_row_distribution(csr: TransitionCSR, at: AliasTables, row: int) -> dic
     """Exact distribution the device draws from for ``row`` (for tests): {column: probability}."""
     if at.layout == "compact":
         w0, base = int(at.rowinfo[row, 0]), int(at.rowinfo[row, 1])
-        off, n = w0 & 0xFFFFF, (w0 >> 20) & 0x3FF
+        off, n = w0 & 0x7FFF, (w0 >> ROW_N_SHIFT) & 0x3FF
     else:
         off, n, base = (int(x) for x in at.rowinfo[row, :3])
     out: dict = {}

@@ -47,8 +47,8 @@ def _decode_alias(at):
     """AliasTables -> (off[n_rows], n[n_rows], base[n_rows], cls[n_rows], thresh, a, b)."""
     ri = at.rowinfo
     if at.layout == "compact":
-        off = (ri[:, 0] & 0xFFFFF).astype(np.int64)
-        n = ((ri[:, 0] >> 20) & 0x3FF).astype(np.int64)
+        off = (ri[:, 0] & 0x7FFF).astype(np.int64)
+        n = ((ri[:, 0] >> 15) & 0x3FF).astype(np.int64)
         cls = (ri[:, 0] >> 30).astype(np.int64)
         base = ri[:, 1].astype(np.int64)
         th = at.alias[:, 0].astype(np.uint32)

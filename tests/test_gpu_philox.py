@@ -298,12 +298,15 @@ def test_errors(engine, c1_csr, tmp_path):
 def k1_env(monkeypatch):
     def set_variant(variant):
         monkeypatch.delenv("NRW_K1", raising=False)
+        monkeypatch.delenv("NRW_DET", raising=False)
         if variant == "general":
             monkeypatch.setenv("NRW_K1", "general")
+        elif variant == "fast_nodet":
+            monkeypatch.setenv("NRW_DET", "0")
     return set_variant
 
 
-@pytest.mark.parametrize("variant", ["fast", "general"])
+@pytest.mark.parametrize("variant", ["fast", "fast_nodet", "general"])
 def test_score_fast_path_bit_exact_all_variants(engine, c1_csr, k1_env, variant):
     """walk_score_kernel and the general kernel produce the same integers as the numpy port:
     identity and packed class weights, ragged starts with the sink and empty starts in the list,
@@ -314,7 +317,7 @@ def test_score_fast_path_bit_exact_all_variants(engine, c1_csr, k1_env, variant)
     _, nc1, _ = _classes(c1_csr, mesh.source_default)                    # classes {0, 1}
     nc3 = (np.arange(c1_csr.n_rows) % 4).astype(np.uint8)                # classes {0, 1, 2, 3}
     nc3[900] = 2                                                         # a weighted sink
-    want = {"fast": "walk_score<TAB_SMEM", "general": "walk_philox<"}[variant]
+    want = {"fast": "walk_score<TAB_SMEM", "fast_nodet": "walk_score<TAB_SMEM", "general": "walk_philox<"}[variant]
     starts = np.array([435, 0, 900, 14, 14, 899, 450, 16, 464])
     counts = np.array([3000, 0, 17, 1, 333, 64, 5, 2500, 1200])
     total = int(counts.sum())
@@ -328,8 +331,9 @@ def test_score_fast_path_bit_exact_all_variants(engine, c1_csr, k1_env, variant)
                               start_id_base=idb)
             if nt >= 2:
                 assert want in res.kernel, res.kernel
-                if variant == "fast":
-                    assert res.kernel.endswith("true>" if idw else "false>"), res.kernel
+                if variant != "general":
+                    assert (",true," if idw else ",false,") in res.kernel, res.kernel
+                    assert res.kernel.endswith(",true>" if variant == "fast" else ",false>"), res.kernel
             else:
                 assert "walk_philox<" in res.kernel                      # nt = 1: no step at all
             port = philox_port.walk_port(c1_csr, starts, counts, nt, 5, alias=tabs.alias_host, class_value=cv,
@@ -368,10 +372,45 @@ def test_score_fast_path_equals_general_kernel_at_full_size(engine, k1_env):
     _, nc, _ = _classes(csr, mesh.source_default)
     tabs = engine.upload(csr, node_class=nc)
     out = {}
-    for variant in ("fast", "general"):
+    for variant in ("fast", "fast_nodet", "general"):
         k1_env(variant)
         r = engine.walk(tabs, np.arange(10000), 1000, 30000, 3, score=True, class_value=[0, 1, 0, 0])
         out[variant] = (r.score.cpu().numpy(), r.counters_dict(), r.kernel)
     assert "walk_score<" in out["fast"][2] and "walk_philox<" in out["general"][2]
-    assert np.array_equal(out["fast"][0], out["general"][0])
-    assert out["fast"][1] == out["general"][1]
+    for v in ("fast", "fast_nodet"):
+        assert np.array_equal(out[v][0], out["general"][0])
+        assert out[v][1] == out["general"][1]
+
+
+def test_deterministic_rows_on_a_general_graph(engine, k1_env):
+    """Single-successor rows of every kind: successor absorbing (folded without a draw), successor
+    live (stepped normally), chains of them, a deterministic start, weighted absorbing rows."""
+    from nrw import mesh, tables
+    from oracle import philox_port
+    rng = np.random.default_rng(12)
+    n = 60
+    q = np.zeros((n, n))
+    for i in range(n):
+        k = int(rng.integers(2, 7))
+        cols = rng.choice(n, size=k, replace=False)
+        q[i, cols] = rng.dirichlet(np.ones(k))
+    q[50:] = 0                                   # rows 50..59 absorbing
+    for r, tgt in ((5, 55), (6, 5), (7, 6), (8, 59), (9, 20), (10, 10)):
+        q[r] = 0; q[r, tgt] = 1.0                # 5 -> sink, 6 -> 5 -> sink, 7 -> 6 -> ..., 9 -> live row, 10 self loop
+    csr = mesh.csr_from_dense(q, n_live=50)
+    nc = (np.arange(n) % 4).astype(np.uint8)
+    at = tables.build_alias(csr, node_class=nc)
+    w0 = at.rowinfo[:, 0]
+    detabs = (w0 >> 27) & 1
+    assert detabs[5] == 1 and detabs[8] == 1 and detabs[6] == 0 and detabs[9] == 0 and detabs[10] == 0
+    assert ((w0[5] >> 25) & 3) == nc[55] and ((w0[8] >> 25) & 3) == nc[59]
+    tabs = engine.upload(csr, node_class=nc)
+    starts = np.array([0, 5, 6, 7, 8, 9, 10, 3, 55, 21])
+    counts = np.array([4000, 300, 300, 300, 77, 300, 50, 4000, 9, 2000])
+    for variant in ("fast", "fast_nodet", "general"):
+        k1_env(variant)
+        for cv in ([0, 1, 2, 3], [3, 0, 200, 7]):
+            for nt in (40, 2, 3, 4):
+                res = engine.walk(tabs, starts, counts, nt, 31, score=True, class_value=cv)
+                port = philox_port.walk_port(csr, starts, counts, nt, 31, alias=tabs.alias_host, class_value=cv)
+                _cmp(res, port, hist=False)
