@@ -24,7 +24,7 @@ import numpy as np
 
 sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
 import utils.logging_utils as utils       # noqa: E402
-from nrw import dropin, mesh               # noqa: E402
+from nrw import dist as ndist, dropin, mesh   # noqa: E402
 from nrw.fluence import solve_fluence      # noqa: E402
 
 rw_logger = logging.getLogger("NRW")
@@ -83,6 +83,7 @@ def run(args):
     source = mesh.SOURCES[args.get('source', 'default')] if args.get('source', 'default') != 'default' \
         else sourceTerm
 
+    rank, world = ndist.init_from_env()        # under torchrun: one process per GPU, rank 0 writes the files
     try:
         csr = mesh.build_fluence_csr(dt, da, v, SigS, L)              # :279-381
     except ValueError:
@@ -94,13 +95,15 @@ def run(args):
     m = csr.meta['mesh']
     meshSize, NS, ND = m['meshSize'], m['NS'], m['ND']
     rw_logger.info('Mesh Size: {}'.format(meshSize))
-    if csr.n_rows <= mesh.MAX_DENSE_CSV_ROWS:
-        mesh.save_matrix_csv(matrix_filename, csr)                    # :384, byte-identical text
-    else:
+    if csr.n_rows > mesh.MAX_DENSE_CSV_ROWS:
         matrix_filename = os.path.splitext(matrix_filename)[0] + '.npz'
-        mesh.save_matrix_npz(matrix_filename, csr)
-        rw_logger.warning("matrix has {} rows: saved as CSR in {} instead of a dense CSV".format(
-            csr.n_rows, matrix_filename))
+    if rank == 0 or rmode != 'pc':
+        if csr.n_rows <= mesh.MAX_DENSE_CSV_ROWS:
+            mesh.save_matrix_csv(matrix_filename, csr)                # :384, byte-identical text
+        else:
+            mesh.save_matrix_npz(matrix_filename, csr)
+            rw_logger.warning("matrix has {} rows: saved as CSR in {} instead of a dense CSV".format(
+                csr.n_rows, matrix_filename))
     rw_logger.info("Transition matrix construction complete")
     rw_logger.info("    matrix saved to {}".format(matrix_filename))
 
@@ -141,10 +144,11 @@ def run(args):
             rwSol[posind, aind] = tempval / M
     rw_logger.info("Simulation using {} completed on {}".format(rmode, datetime.now()))
 
-    if args['plot_results']:
-        plot_results(rwSol, m['dirs'], m['space'], results_filename)
-    np.savetxt(results_filename, rwSol, delimiter=",")                # :446
-    rw_logger.info("Solution saved to {}".format(results_filename))
+    if rank == 0:
+        if args['plot_results']:
+            plot_results(rwSol, m['dirs'], m['space'], results_filename)
+        np.savetxt(results_filename, rwSol, delimiter=",")            # :446
+        rw_logger.info("Solution saved to {}".format(results_filename))
     return rwSol
 
 

@@ -68,3 +68,16 @@ def allreduce_sum_(tensors):
         if t is not None:
             dist.all_reduce(t, op=dist.ReduceOp.SUM)
     return tensors
+
+
+def broadcast_int(value: int, src: int = 0) -> int:
+    """Rank ``src``'s value on every rank (the Philox seed: with the reference's time-based default
+    seed, fluence_mini_app.py:517-521, every process would otherwise draw its own)."""
+    import torch
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
+        return int(value)
+    dev = torch.device("cuda", torch.cuda.current_device()) if dist.get_backend() == "nccl" else torch.device("cpu")
+    t = torch.tensor([int(value)], dtype=torch.int64, device=dev)
+    dist.broadcast(t, src=src)
+    return int(t.item())

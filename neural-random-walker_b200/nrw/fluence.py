@@ -74,6 +74,7 @@ def solve_fluence(csr: _mesh.TransitionCSR, M: int, nt: int, SigA, dt, v, source
     if seed is None:
         from .dropin import philox_seed_from_global_stream
         seed = philox_seed_from_global_stream()
+    seed = _dist.broadcast_int(seed)                      # one seed for all ranks
     n_classes = int((class_value != 0).sum())
     uniform_time = (float(SigA) == 0.0) and n_classes <= 1
     if uniform_time:

@@ -21,7 +21,7 @@ import numpy as np
 
 sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
 import utils.logging_utils as utils       # noqa: E402
-from nrw import dropin, mesh               # noqa: E402
+from nrw import dist as ndist, dropin, mesh   # noqa: E402
 from nrw.engine import get_engine          # noqa: E402
 
 rw_logger = logging.getLogger("NRW")
@@ -72,10 +72,14 @@ def _counts_pc_fused(csr, M, nt, n_cols, rng, sampler):
             keep = (k[sl] < 2) & (t[sl] < n_cols)
             td[s, k[sl][keep], t[sl][keep]] = c[sl][keep]
         return td, rep.draws_used, mode
-    seed = dropin.philox_seed_from_global_stream()
+    seed = ndist.broadcast_int(dropin.philox_seed_from_global_stream())
     nt_k = max(min(int(nt), n_cols), 1)       # steps past the reported window cannot change it
-    res = eng.walk(tabs, [0, 1], [M, M], nt_k, seed, sampler=sampler, count_tn=True, t_cap=nt_k,
-                   count_per_start=True)
+    # every rank walks its slice of both start states' walkers; one all-reduce of the counts
+    rank, world = ndist.world()
+    lo, hi = ndist.shard_range(int(M), rank, world)
+    res = eng.walk(tabs, [0, 1], [hi - lo, hi - lo], nt_k, seed, sampler=sampler, count_tn=True,
+                   t_cap=nt_k, count_per_start=True, start_id_base=[lo, int(M) + lo])
+    ndist.allreduce_sum_([res.count_tn, res.counters])
     cnt = res.count_tn.cpu().numpy()          # [2, t_cap, 3]
     td[:, :, :nt_k] = np.transpose(cnt[:, :, :2], (0, 2, 1))
     td[0, 0, 0] = M
@@ -101,7 +105,9 @@ def run(args):
                         "1-(SigA+SigS)*dt*exp(-(SigA+SigS)*dt)-exp(-(SigA+SigS)*dt)<=0.01.")
         raise
     meshSize = 2
-    np.savetxt(matrix_filename, myQ, delimiter=",")                           # :290
+    rank, world = ndist.init_from_env()        # under torchrun: one process per GPU, rank 0 writes the files
+    if rank == 0 or rmode != 'pc':
+        np.savetxt(matrix_filename, myQ, delimiter=",")                       # :290
     rw_logger.info("Transition matrix construction complete")
     rw_logger.info("    matrix saved to {}".format(matrix_filename))
 
@@ -139,10 +145,11 @@ def run(args):
             rwSol[i, :maxT] = (initp * tempdata[0, :maxT] + initn * tempdata[1, :maxT]) / M
     rw_logger.info("Simulation using {} completed on {}".format(rmode, datetime.now()))
 
-    if args['plot_results']:
-        plot_results(rwSol, maxT, args)
-    np.savetxt(results_filename, rwSol, delimiter=",")                        # :358
-    rw_logger.info("Solution saved to {}".format(results_filename))
+    if rank == 0:
+        if args['plot_results']:
+            plot_results(rwSol, maxT, args)
+        np.savetxt(results_filename, rwSol, delimiter=",")                    # :358
+        rw_logger.info("Solution saved to {}".format(results_filename))
     return rwSol
 
 

@@ -1,0 +1,57 @@
+"""Two ranks on two B200s through the drop-in command lines (torchrun): the sharded Philox solve and
+its single NCCL all-reduce must reproduce the single-process result bit for bit (integer tallies,
+same stream ids).  Skipped on a one-GPU box; the CPU suite covers the same host logic over gloo
+(tests/test_dist_gloo.py)."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from conftest import PKG
+
+pytestmark = pytest.mark.gpu
+
+
+def _two_gpus():
+    import torch
+    return torch.cuda.is_available() and torch.cuda.device_count() >= 2
+
+
+def _torchrun(script, argv, port):
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+           "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.join(PKG, script)] + argv
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-3000:]
+
+
+@pytest.mark.skipif(not _two_gpus(), reason="needs 2 GPUs")
+def test_fluence_cli_two_ranks_equals_one(tmp_path):
+    import fluence_mini_app as app
+    common = ["-r", "pc", "--rng", "philox", "-M", "1001", "-nt", "64", "--rand_seed", "3", "-sa", "0.4"]
+    two = ["--matrix_filename", str(tmp_path / "m2.csv"), "--results_filename", str(tmp_path / "r2.csv"),
+           "--log_file", str(tmp_path / "log2" / "x.log")]
+    _torchrun("fluence_mini_app.py", common + two, 29631)
+    a = vars(app.build_parser().parse_args(common))
+    a.update(matrix_filename=str(tmp_path / "m1.csv"), results_filename=str(tmp_path / "r1.csv"))
+    np.random.seed(3)
+    one = app.run(a)
+    got = np.genfromtxt(str(tmp_path / "r2.csv"), delimiter=",")
+    assert np.array_equal(got, np.genfromtxt(str(tmp_path / "r1.csv"), delimiter=","))
+    assert np.array_equal(got, one) and got.any()
+
+
+@pytest.mark.skipif(not _two_gpus(), reason="needs 2 GPUs")
+def test_simple_flux_cli_two_ranks_equals_one(tmp_path):
+    import simple_flux_miniapp as app
+    common = ["-r", "pc", "--rng", "philox", "-M", "200001", "--rand_seed", "5", "--use_sinks"]
+    two = ["--matrix_filename", str(tmp_path / "m2.csv"), "--results_filename", str(tmp_path / "r2.csv"),
+           "--log_file", str(tmp_path / "log2" / "x.log")]
+    _torchrun("simple_flux_miniapp.py", common + two, 29632)
+    a = vars(app.build_parser().parse_args(common))
+    a.update(matrix_filename=str(tmp_path / "m1.csv"), results_filename=str(tmp_path / "r1.csv"))
+    np.random.seed(5)
+    one = app.run(a)
+    got = np.genfromtxt(str(tmp_path / "r2.csv"), delimiter=",")
+    assert got.shape == (2, 1002) and np.array_equal(got, one)
