@@ -234,8 +234,7 @@ def main(argv=None):
         if args['run_mode'] == 'loihi' or args['fugu_backend'] == 'loihi':
             raise SystemExit('\n *** NxSDK package is not installed. Running RandomWalk on Loihi is unavailable. *** \n')
     log_file = os.path.expanduser(args['log_file'])
-    if not os.path.exists(os.path.dirname(log_file)):
-        os.makedirs(os.path.dirname(log_file))
+    os.makedirs(os.path.dirname(log_file), exist_ok=True)        # (several ranks may start at once)
     utils.setup_logging(log_file=log_file, useLogFile=True, log_level=args['loglevel'])
     rw_logger.info('Using config: {}'.format(args))
     rw_logger.info('Starting run on {}'.format(datetime.now()))

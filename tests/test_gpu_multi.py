@@ -23,7 +23,9 @@ def _torchrun(script, argv, port):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
            "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.join(PKG, script)] + argv
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
-    assert r.returncode == 0, r.stderr[-3000:]
+    if r.returncode != 0:
+        tb = r.stderr.find("Traceback")
+        raise AssertionError(r.stderr[tb:tb + 3000] if tb >= 0 else r.stderr[-3000:])
 
 
 @pytest.mark.skipif(not _two_gpus(), reason="needs 2 GPUs")
