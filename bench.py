@@ -395,8 +395,10 @@ def run_ours(args):
                        "steps": n_e2e, "entry": "nrw_fluence_scores_host (pinned host buffers)"}
         line["clocks"] = clk.summary()
 
-    # ---- side legs on rank 0 at N=1: BASELINE config C2 + fluence error, cpu_baseline -----------
+    # ---- side legs on rank 0 at N=1: resource rooflines, BASELINE config C2 + fluence error, cpu_baseline
     if rank == 0 and world == 1 and not args.no_extras:
+        line["resources"] = resource_leg(eng, tabs, starts, Mg, id_base, flush, steps_per_launch, kernel_ms,
+                                         line["roofline"]["deterministic_step_fraction"])
         line["c2"] = c2_leg(eng)
         cb = cpu_leg(args.cpu_seconds)
         cb.pop("walker_steps"); cb.pop("seconds")
@@ -409,6 +411,44 @@ def run_ours(args):
     if world > 1:
         tdist.barrier()
         tdist.destroy_process_group()
+
+
+def resource_leg(eng, tabs, starts, Mg, id_base, flush, steps_per_launch, kernel_ms, det_frac):
+    """The memory/atomic rooflines named by BASELINE north_star: rates of the resources the walk
+    touches, measured by micro-benchmarks at the walk's own launch geometry (nrw_microbench), next
+    to the rates the walk kernels reach.  None of them is the binding resource (issue slots are)."""
+    import torch
+    peaks = {"smem_random_load_8B_per_s": eng.microbench("smem_load", 20000),
+             "smem_random_atomic_per_s": eng.microbench("smem_atomic", 10001),
+             "l2_random_load_8B_per_s": eng.microbench("l2_load", 158761),
+             "global_random_atomic_per_s": eng.microbench("global_atomic", 10001, iters=200)}
+    out = {"measured_peaks": peaks,
+           "how": "nrw_microbench: one 1024-thread CTA per SM, random indices from a per-thread LCG, "
+                  "dependent loads; best of 5 event-timed launches"}
+    # score kernel: two dependent shared-memory look-ups per drawn step (alias entry, row descriptor)
+    lds = 2.0 * steps_per_launch * (1.0 - det_frac) / (kernel_ms * 1e-3)
+    out["score_kernel"] = {"smem_loads_per_s": lds, "frac_of_smem_load_peak": lds / peaks["smem_random_load_8B_per_s"]}
+    # occupancy-histogram mode: one shared-memory atomic per walker-step (sink arrivals are vote-aggregated)
+    hl, hres = eng.prepare_walk(tabs, starts, Mg, NT, seed=1, score=True, class_value=[0, 1, 0, 0],
+                                node_hist=True, start_id_base=id_base)
+    for _ in range(3):
+        hl()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(10)]
+    for a, b in ev:
+        flush.fill_(1)
+        hl.zero()
+        a.record()
+        hl.launch_kernel()
+        b.record()
+    torch.cuda.synchronize()
+    ms = float(np.mean([a.elapsed_time(b) for a, b in ev]))
+    hist = hres.node_hist.cpu().numpy()
+    atomics = float(hist[:-1].sum())
+    out["hist_kernel"] = {"kernel": hres.kernel, "kernel_ms": ms,
+                          "walker_steps_per_s": steps_per_launch / (ms * 1e-3),
+                          "smem_atomics_per_s": atomics / (ms * 1e-3),
+                          "frac_of_smem_atomic_peak": atomics / (ms * 1e-3) / peaks["smem_random_atomic_per_s"]}
+    return out
 
 
 def c2_leg(eng):

@@ -205,6 +205,15 @@ NRW_API int  nrw_fluence_scores_host(nrw_engine* e,
                              int64_t* score_host, unsigned long long* counters_host,
                              void* stream);
 
+/* Roofline denominators measured on the engine's device at the walk's own launch geometry (one
+ * 1024-thread CTA per SM): kind 0 = random atomicAdd on a per-CTA shared-memory histogram of n bins,
+ * 1 = dependent random 8-byte shared-memory loads from n entries, 2 = dependent random 8-byte loads
+ * from an n-entry global table (device pointer `table`, L2-resident for n*8 B << 126 MB), 3 = random
+ * 64-bit atomicAdd on a global histogram `hist` of n bins.  Every thread performs `iters`
+ * operations; time the launch with events on `stream`.  `scratch` = 8 device bytes.               */
+NRW_API int  nrw_microbench(nrw_engine* e, int32_t kind, int32_t n, int32_t iters, const void* table,
+                    unsigned long long* hist, unsigned long long* scratch, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -7,6 +7,7 @@
 #include <cstring>
 
 #include "common.cuh"
+#include "microbench.cuh"
 #include "post.cuh"
 #include "walk_philox.cuh"
 #include "walk_replay.cuh"
@@ -424,5 +425,31 @@ extern "C" int nrw_fluence_scores_host(nrw_engine* e, int32_t n_rows, int32_t n_
         CUDA_TRY(cudaMemcpyAsync(counters_host, e->d_counters, NRW_N_COUNTERS * sizeof(unsigned long long),
                                  cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaStreamSynchronize(st));
+    return NRW_OK;
+}
+
+// ---- roofline denominators ----------------------------------------------------------------------
+extern "C" int nrw_microbench(nrw_engine* e, int32_t kind, int32_t n, int32_t iters, const void* table,
+                              unsigned long long* hist, unsigned long long* scratch, void* stream) {
+    if (!e || n <= 0 || iters <= 0 || !scratch) return fail(NRW_EINVAL, "nrw_microbench: bad argument");
+    cudaStream_t st = (cudaStream_t)stream;
+    CUDA_TRY(cudaSetDevice(e->device));
+    const int grid = e->n_sms;
+    int smem = 0;
+    const void* fn = nullptr;
+    switch (kind) {
+        case MB_SMEM_ATOMIC: fn = (const void*)microbench_kernel<MB_SMEM_ATOMIC>; smem = align16(n * 4); break;
+        case MB_SMEM_LOAD:   fn = (const void*)microbench_kernel<MB_SMEM_LOAD>;   smem = align16(n * 8); break;
+        case MB_L2_LOAD:     fn = (const void*)microbench_kernel<MB_L2_LOAD>;
+            if (!table) return fail(NRW_EINVAL, "nrw_microbench: L2 load needs a table"); break;
+        case MB_GLOBAL_ATOMIC: fn = (const void*)microbench_kernel<MB_GLOBAL_ATOMIC>;
+            if (!hist) return fail(NRW_EINVAL, "nrw_microbench: global atomics need a histogram"); break;
+        default: return fail(NRW_EINVAL, "nrw_microbench: kind=%d", kind);
+    }
+    if (smem > e->max_smem) return fail(NRW_ENOSPC, "nrw_microbench: %d B of shared memory", smem);
+    CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem > 0 ? smem : 16));
+    const uint2* tab = (const uint2*)table;
+    void* args[] = {&n, &iters, &tab, &hist, &scratch};
+    CUDA_TRY(cudaLaunchKernel(fn, dim3(grid), dim3(1024), args, smem, st));
     return NRW_OK;
 }

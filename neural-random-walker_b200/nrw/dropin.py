@@ -40,8 +40,8 @@ def resolve_rng(mode, total_walkers: int) -> str:
 def device_tables(csr, node_class=None, key=None):
     """Upload (once) and cache the device tables of a matrix."""
     eng = get_engine()
-    k = (id(csr) if key is None else key, None if node_class is None else node_class.tobytes(),
-         eng.device.index)
+    k = (id(csr), None if node_class is None else node_class.tobytes(), eng.device.index) \
+        if key is None else (key, eng.device.index)
     hit = _table_cache.get(k)
     if hit is None:
         if len(_table_cache) > 8:

@@ -63,7 +63,7 @@ _lib = None
 EXPORTS = ("nrw_abi_version", "nrw_last_error", "nrw_create", "nrw_destroy", "nrw_device_info",
            "nrw_build_cum", "nrw_walk_philox", "nrw_walk_philox_plan", "nrw_walk_replay",
            "nrw_assemble_events", "nrw_expand_events", "nrw_expand_counts",
-           "nrw_fluence_scores_host")
+           "nrw_fluence_scores_host", "nrw_microbench")
 
 
 def load_library():
@@ -93,6 +93,7 @@ def load_library():
     lib.nrw_expand_counts.argtypes = [vp, vp, i32, i32, i32, i32, i64, vp, vp]
     lib.nrw_fluence_scores_host.argtypes = [vp, i32, i32, i32, vp, vp, i32, vp, vp, i64, i64, u64,
                                             i32, C.POINTER(dbl * 4), vp, vp, vp]
+    lib.nrw_microbench.argtypes = [vp, i32, i32, i32, vp, vp, vp, vp]
     for name in EXPORTS:
         fn = getattr(lib, name)
         if name != "nrw_last_error":
@@ -475,6 +476,32 @@ class Engine:
                                                int(nt), int(start_node), int(start_count), _ptr(out),
                                                self.stream))
         return out
+
+    # ------------------------------------------------------------------ roofline denominators
+    MICROBENCH_KINDS = {"smem_atomic": 0, "smem_load": 1, "l2_load": 2, "global_atomic": 3}
+
+    def microbench(self, kind: str, n: int, iters: int = 2000, reps: int = 5) -> float:
+        """Operations per second of one resource at the walk's launch geometry (see include/nrw.h,
+        nrw_microbench): best of ``reps`` event-timed launches."""
+        torch = self.torch
+        k = self.MICROBENCH_KINDS[kind]
+        table = hist = None
+        if kind == "l2_load":
+            g = torch.Generator(device="cpu").manual_seed(1)
+            table = torch.randint(0, 2 ** 31 - 1, (int(n), 2), dtype=torch.int32, generator=g).to(self.device)
+        if kind == "global_atomic":
+            hist = torch.zeros(int(n), dtype=torch.int64, device=self.device)
+        scratch = torch.zeros(1, dtype=torch.int64, device=self.device)
+        best = float("inf")
+        for _ in range(reps + 1):                              # first launch = warm-up
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            self._check(self.lib.nrw_microbench(self.handle, k, int(n), int(iters), _ptr(table), _ptr(hist),
+                                                _ptr(scratch), self.stream))
+            b.record()
+            b.synchronize()
+            best = min(best, a.elapsed_time(b))
+        return self.n_sms * 1024 * float(iters) / (best * 1e-3)
 
     # ------------------------------------------------------------------ host-buffer end-to-end
     def fluence_scores_host(self, alias_tables, n_rows, n_live, start_nodes, start_prefix, walker_lo,

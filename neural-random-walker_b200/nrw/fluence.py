@@ -54,7 +54,14 @@ def solve_fluence(csr: _mesh.TransitionCSR, M: int, nt: int, SigA, dt, v, source
     """rwSol for every start node of a fluence mesh built by ``mesh.build_fluence_csr``."""
     m = csr.meta["mesh"]
     meshSize, NS, ND = m["meshSize"], m["NS"], m["ND"]
-    srcvals = _mesh.source_values(m["meshpoints"], source)
+    cache = csr.meta.setdefault("_source_cache", {})          # per-node source values: a Python call per node
+    if source not in cache:
+        sv = _mesh.source_values(m["meshpoints"], source)
+        try:
+            cache[source] = (sv,) + tuple(_tables.classify_source(sv, csr.n_rows))
+        except ValueError:                                    # > 3 distinct values: replay mode can still run
+            cache[source] = (sv, None, None)
+    srcvals, node_class, class_value = cache[source]
     mode = resolve_rng(rng, meshSize * int(M))
     rank, world = _dist.world()
     starts = np.arange(meshSize)
@@ -69,8 +76,9 @@ def solve_fluence(csr: _mesh.TransitionCSR, M: int, nt: int, SigA, dt, v, source
         return FluenceResult(scatter_to_rwsol(per_start, NS, ND), per_start, rep.draws_used, "replay")
 
     # ---- philox: one K1 launch, per-start score in registers -------------------------------
-    node_class, class_value = _tables.classify_source(srcvals, csr.n_rows)
-    eng, tabs = device_tables(csr, node_class=node_class)
+    if node_class is None:
+        _tables.classify_source(srcvals, csr.n_rows)          # raises the explanatory ValueError
+    eng, tabs = device_tables(csr, node_class=node_class, key=(id(csr), "fluence", id(node_class)))
     if seed is None:
         from .dropin import philox_seed_from_global_stream
         seed = philox_seed_from_global_stream()
