@@ -154,7 +154,7 @@ extern "C" int nrw_expand_counts(nrw_engine* e, const uint32_t* count_tn, int32_
 
 // ---- K1: plan + launch ------------------------------------------------------------------------
 struct WalkPlan {
-    int tab, tl, grid, smem;
+    int tab, tl, grid, smem, block;
     WalkParams p;
     const void* fn;
     const char* name;
@@ -276,7 +276,7 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
     if (range > 4096) range = 4096;
     p.range = range;
 
-    plan->fn = nullptr; plan->name = "";
+    plan->fn = nullptr; plan->name = ""; plan->block = WALK_THREADS;
 #define X(TAB, TL)                                                           \
     if (tab == TAB && tl == TL) {                                            \
         plan->fn = (const void*)walk_philox_kernel<TAB, TL>;                 \
@@ -295,13 +295,28 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
         if (!general) {
             // a lane's 32-bit step counter is flushed at every range fetch: keep range * nt < 2^32
             while (p.range > 32 && p.range * (long long)w->nt >= (1ll << 32)) p.range = ((p.range / 2) / 32) * 32;
-#define Y(TAB, IDW, DET)                                                       \
-    if (tab == TAB && idw == IDW && det == DET) {                              \
-        plan->fn = (const void*)walk_score_kernel<TAB, IDW, DET>;              \
-        plan->name = "walk_score<" #TAB "," #IDW "," #DET ">";                 \
+            // two CTAs of 768 threads per SM when the tables leave room (NRW_CPS=1 forces one CTA)
+            const char* cps_env = getenv("NRW_CPS");
+            const int cps = (plan->smem <= 112 * 1024 && !(cps_env && strcmp(cps_env, "1") == 0)) ? 2 : 1;
+#define Y(TAB, IDW, DET, CPS)                                                  \
+    if (tab == TAB && idw == IDW && det == DET && cps == CPS) {                \
+        plan->fn = (const void*)walk_score_kernel<TAB, IDW, DET, CPS>;         \
+        plan->name = "walk_score<" #TAB "," #IDW "," #DET ",cps=" #CPS ">";    \
     }
-            Y(TAB_SMEM, true, true) Y(TAB_SMEM, false, true) Y(TAB_HYB, true, true) Y(TAB_HYB, false, true)
-            Y(TAB_SMEM, true, false) Y(TAB_SMEM, false, false) Y(TAB_HYB, true, false) Y(TAB_HYB, false, false)
+#define Y2(TAB, IDW, DET) Y(TAB, IDW, DET, 1) Y(TAB, IDW, DET, 2)
+            Y2(TAB_SMEM, true, true) Y2(TAB_SMEM, false, true) Y2(TAB_HYB, true, true) Y2(TAB_HYB, false, true)
+            Y2(TAB_SMEM, true, false) Y2(TAB_SMEM, false, false) Y2(TAB_HYB, true, false) Y2(TAB_HYB, false, false)
+#undef Y2
+            if (cps == 2) {
+                plan->block = 768;
+                long long g2 = (n + 767) / 768;
+                if (g2 > 2ll * e->n_sms) g2 = 2ll * e->n_sms;
+                plan->grid = (int)(g2 < 1 ? 1 : g2);
+                long long r2 = n / ((long long)plan->grid * 24 * 8);
+                r2 = (r2 / 32) * 32;
+                p.range = r2 < 32 ? 32 : (r2 > 4096 ? 4096 : r2);
+                while (p.range > 32 && p.range * (long long)w->nt >= (1ll << 32)) p.range = ((p.range / 2) / 32) * 32;
+            }
 #undef Y
         }
     }
@@ -319,7 +334,7 @@ extern "C" int nrw_walk_philox_plan(nrw_engine* e, const nrw_tables* t, const nr
     if (rc) return rc;
     if (name && name_len > 0) { strncpy(name, plan.name, name_len - 1); name[name_len - 1] = 0; }
     if (grid) *grid = plan.grid;
-    if (block) *block = WALK_THREADS;
+    if (block) *block = plan.block;
     if (smem_bytes) *smem_bytes = plan.smem;
     return NRW_OK;
 }
@@ -333,7 +348,7 @@ extern "C" int nrw_walk_philox(nrw_engine* e, const nrw_tables* t, const nrw_wal
     CUDA_TRY(cudaFuncSetAttribute(plan.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, plan.smem));
     CUDA_TRY(cudaMemsetAsync(e->work_next, 0, sizeof(unsigned long long), (cudaStream_t)stream));
     void* args[] = {&plan.p};
-    CUDA_TRY(cudaLaunchKernel(plan.fn, dim3(plan.grid), dim3(WALK_THREADS), args, plan.smem,
+    CUDA_TRY(cudaLaunchKernel(plan.fn, dim3(plan.grid), dim3(plan.block), args, plan.smem,
                               (cudaStream_t)stream));
     return NRW_OK;
 }

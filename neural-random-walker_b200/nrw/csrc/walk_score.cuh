@@ -44,8 +44,10 @@ __device__ __forceinline__ uint2 philox2x32_10_rk(uint32_t c0, uint32_t c1, cons
     return make_uint2(c0, c1);
 }
 
-template <int TAB, bool IDW, bool DET>
-__global__ void __launch_bounds__(WALK_THREADS, 1)
+// CPS = CTAs per SM: 1 -> 1024 threads (tables up to 227 KB), 2 -> two CTAs of 768 threads when the
+// tables fit half an SM's shared memory (48 instead of 32 resident warps).
+template <int TAB, bool IDW, bool DET, int CPS>
+__global__ void __launch_bounds__(CPS == 1 ? 1024 : 768, CPS)
 walk_score_kernel(const __grid_constant__ WalkParams p) {
     static_assert(TAB == TAB_SMEM || TAB == TAB_HYB, "compact alias tables only");
     extern __shared__ __align__(16) unsigned char smem[];

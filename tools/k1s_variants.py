@@ -1,0 +1,54 @@
+#!/usr/bin/env python
+"""A/B timing of the score kernel's launch variants on a mesh (run on a B200).
+Usage: python tools/k1s_variants.py [c1|c5] [walkers_per_node]"""
+import json
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (os.path.join(ROOT, "neural-random-walker_b200"), ROOT):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+
+def main():
+    import torch
+    from nrw import mesh, tables
+    from nrw.engine import Engine
+    which = sys.argv[1] if len(sys.argv) > 1 else "c1"
+    par = dict(c1=(0.01, 1.0 / 15.0), c5=(0.01, 0.02))[which]
+    M = int(sys.argv[2]) if len(sys.argv) > 2 else dict(c1=150000, c5=12500)[which]
+    eng = Engine(0)
+    csr = mesh.build_fluence_csr(par[0], par[1], 200, 0.15, 1)
+    src = mesh.source_values(csr.meta["mesh"]["meshpoints"], mesh.source_default)
+    nc, _ = tables.classify_source(src, csr.n_rows)
+    tabs = eng.upload(csr, node_class=nc)
+    starts = np.arange(csr.n_live)
+    flush = torch.empty(512 << 20, dtype=torch.uint8, device=eng.device)
+    for tag, env in (("default", {}), ("cps1", {"NRW_CPS": "1"}), ("always_draw", {"NRW_DET": "0"}),
+                     ("general", {"NRW_K1": "general"})):
+        for k in ("NRW_CPS", "NRW_DET", "NRW_K1"):
+            os.environ.pop(k, None)
+        os.environ.update(env)
+        launch, res = eng.prepare_walk(tabs, starts, M, 30000, seed=1, score=True, class_value=[0, 1, 0, 0])
+        for _ in range(3):
+            launch()
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(10)]
+        for a, b in ev:
+            flush.fill_(1)
+            launch.zero()
+            a.record()
+            launch.launch_kernel()
+            b.record()
+        torch.cuda.synchronize()
+        ms = float(np.mean([a.elapsed_time(b) for a, b in ev]))
+        steps = int(res.counters.cpu()[0].item())
+        print(json.dumps({"mesh": which, "M": M, "variant": tag, "kernel": res.kernel, "geometry": res.launch_geometry,
+                          "kernel_ms": ms, "walker_steps": steps, "walker_steps_per_s": steps / (ms * 1e-3),
+                          "score_sum": int(res.score.sum().item())}), flush=True)
+
+
+if __name__ == "__main__":
+    main()
