@@ -197,6 +197,7 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
     p.lo = w->walker_lo; p.hi = w->walker_hi;
     p.key = seed_to_key(w->seed); p.nt = w->nt;
     for (int r = 0; r < 10; ++r) p.rk[r] = p.key + (uint32_t)r * PHILOX_W32;
+    p.t_last = w->nt - 1;
     p.score = (long long*)w->score; p.score_sq = w->score_sq; p.tw = w->time_weight;
     p.cwpack = 0;
     for (int i = 0; i < 4; ++i) {

@@ -37,6 +37,7 @@ struct WalkParams {
     long long lo, hi;
     uint32_t key; int nt;
     uint32_t rk[10];                             // Philox round keys key + r * W32
+    int t_last;                                  // nt - 1
     long long* score; double* score_sq;
     uint32_t cwpack; double cv[4]; const double* tw;
     unsigned long long* node_hist;

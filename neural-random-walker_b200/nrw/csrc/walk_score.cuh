@@ -60,7 +60,7 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
     mbar_wait(bar, 0);
     __syncthreads();
 
-    const int t_last = p.nt - 1;                 // last model step (fluence_mini_app.py:236); >= 1 here
+    const int t_last = p.t_last;                 // nt - 1: last model step (fluence_mini_app.py:236); >= 1 here
     const uint32_t lt_mask = lanemask_lt();
 
     // ---- the lane's walker --------------------------------------------------------------------------

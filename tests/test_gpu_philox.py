@@ -299,6 +299,9 @@ def k1_env(monkeypatch):
     def set_variant(variant):
         monkeypatch.delenv("NRW_K1", raising=False)
         monkeypatch.delenv("NRW_DET", raising=False)
+        monkeypatch.delenv("NRW_CPS", raising=False)
+        if variant == "fast_cps1":
+            monkeypatch.setenv("NRW_CPS", "1")
         if variant == "general":
             monkeypatch.setenv("NRW_K1", "general")
         elif variant == "fast_nodet":
@@ -306,7 +309,7 @@ def k1_env(monkeypatch):
     return set_variant
 
 
-@pytest.mark.parametrize("variant", ["fast", "fast_nodet", "general"])
+@pytest.mark.parametrize("variant", ["fast", "fast_cps1", "fast_nodet", "general"])
 def test_score_fast_path_bit_exact_all_variants(engine, c1_csr, k1_env, variant):
     """walk_score_kernel and the general kernel produce the same integers as the numpy port:
     identity and packed class weights, ragged starts with the sink and empty starts in the list,
@@ -317,7 +320,7 @@ def test_score_fast_path_bit_exact_all_variants(engine, c1_csr, k1_env, variant)
     _, nc1, _ = _classes(c1_csr, mesh.source_default)                    # classes {0, 1}
     nc3 = (np.arange(c1_csr.n_rows) % 4).astype(np.uint8)                # classes {0, 1, 2, 3}
     nc3[900] = 2                                                         # a weighted sink
-    want = {"fast": "walk_score<TAB_SMEM", "fast_nodet": "walk_score<TAB_SMEM", "general": "walk_philox<"}[variant]
+    want = "walk_philox<" if variant == "general" else "walk_score<TAB_SMEM"
     starts = np.array([435, 0, 900, 14, 14, 899, 450, 16, 464])
     counts = np.array([3000, 0, 17, 1, 333, 64, 5, 2500, 1200])
     total = int(counts.sum())
@@ -333,7 +336,8 @@ def test_score_fast_path_bit_exact_all_variants(engine, c1_csr, k1_env, variant)
                 assert want in res.kernel, res.kernel
                 if variant != "general":
                     assert (",true," if idw else ",false,") in res.kernel, res.kernel
-                    assert res.kernel.endswith(",true>" if variant == "fast" else ",false>"), res.kernel
+                    assert (",false,cps=" if variant == "fast_nodet" else ",true,cps=") in res.kernel, res.kernel
+                    assert res.kernel.endswith("cps=1>" if variant == "fast_cps1" else "cps=2>"), res.kernel
             else:
                 assert "walk_philox<" in res.kernel                      # nt = 1: no step at all
             port = philox_port.walk_port(c1_csr, starts, counts, nt, 5, alias=tabs.alias_host, class_value=cv,
