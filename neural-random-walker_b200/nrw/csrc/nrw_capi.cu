@@ -294,8 +294,15 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
         const char* det_env = getenv("NRW_DET");             // NRW_DET=0: draw on deterministic rows too
         const bool det = !(det_env && strcmp(det_env, "0") == 0);
         if (!general) {
-            // a lane's 32-bit step counter is flushed at every range fetch: keep range * nt < 2^32
-            while (p.range > 32 && p.range * (long long)w->nt >= (1ll << 32)) p.range = ((p.range / 2) / 32) * 32;
+            // a lane's 32-bit step and score sums are flushed at every range fetch: keep
+            // range * nt * (largest per-step weight) < 2^31
+            long long maxw = 3;                                  // IDW: the weight is the class index
+            if (!idw)
+                for (int i = 0; i < 4; ++i) {
+                    const long long wi = (long long)((p.cwpack >> (8 * i)) & 0xffu);
+                    if (wi > maxw) maxw = wi;
+                }
+            while (p.range > 32 && p.range * (long long)w->nt * maxw >= (1ll << 31)) p.range = ((p.range / 2) / 32) * 32;
             // two CTAs of 768 threads per SM when the tables leave room (NRW_CPS=1 forces one CTA)
             const char* cps_env = getenv("NRW_CPS");
             const int cps = (plan->smem <= 112 * 1024 && !(cps_env && strcmp(cps_env, "1") == 0)) ? 2 : 1;
@@ -316,7 +323,7 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
                 long long r2 = n / ((long long)plan->grid * 24 * 8);
                 r2 = (r2 / 32) * 32;
                 p.range = r2 < 32 ? 32 : (r2 > 4096 ? 4096 : r2);
-                while (p.range > 32 && p.range * (long long)w->nt >= (1ll << 32)) p.range = ((p.range / 2) / 32) * 32;
+                while (p.range > 32 && p.range * (long long)w->nt * maxw >= (1ll << 31)) p.range = ((p.range / 2) / 32) * 32;
             }
 #undef Y
         }

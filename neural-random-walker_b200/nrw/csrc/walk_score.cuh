@@ -9,9 +9,10 @@
 //     absorbing starts) sits behind warp-uniform or [[unlikely]] branches;
 //   * the Philox round keys come from the kernel parameters (constant-bank operands), not from
 //     uniform-register arithmetic repeated every iteration;
-//   * the score is added unconditionally each step and the step t = nt-1 (outside the solution sum,
-//     fluence_mini_app.py:428) is taken back out on the rare end-of-time path; walker-steps are
-//     accumulated as lifetimes at death instead of once per step;
+//   * the score is a per-lane running sum over the lane's walkers (flushed when the start node
+//     changes and at every range fetch), added to unconditionally each step; the step t = nt-1
+//     (outside the solution sum, fluence_mini_app.py:428) is taken back out on the rare end-of-time
+//     path; walker-steps are accumulated as lifetimes at death instead of once per step;
 //   * IDW: class weights equal to the class index turn the weight lookup into one LEA.HI;
 //   * DET: a row whose single successor is absorbing (every exit row of the fluence mesh: 45 % of
 //     all walker-steps) is stepped without computing a draw -- slot 0 with threshold 2^32-1 is taken
@@ -65,7 +66,7 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
 
     // ---- the lane's walker --------------------------------------------------------------------------
     int t = -1;                                  // steps taken; -1 = no walker
-    uint32_t c0 = 0, chi = 0, ra = 0, rb = 0, x = 0;
+    uint32_t c0 = 0, chi = 0, ra = 0, rb = 0;
     // ---- the start the lane accumulates for (changes on the cold path only) -----------------------
     int s = -1;
     long long s_end = 0, sid_base = 0;
@@ -73,7 +74,8 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
     int t_init = 0;
     uint32_t det_w = 0, det_n = 0;               // DET: walkers of a deterministic-exit start
     uint2 srow = make_uint2(0, 0);
-    long long acc = 0;
+    uint32_t x = 0;                              // score of the lane's walkers of start s since the last flush
+                                                 // (flushed at a range fetch once it passes 2^31; planner bound: range * nt * weight < 2^31)
     uint32_t nst = 0, nsurv = 0;                 // nst: < 2^32 between range fetches (range * nt bound)
     unsigned long long nsteps = 0;
     // ---- warp-uniform id range [rbase + cur, rbase + end) ------------------------------------------
@@ -86,9 +88,9 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
         return IDW ? cls : ((p.cwpack >> (cls * 8u)) & 0xffu);
     };
     auto flush_score = [&]() {
-        if (s >= 0 && acc != 0)
-            atomicAdd(reinterpret_cast<unsigned long long*>(p.score) + s, (unsigned long long)acc);
-        acc = 0;
+        if (s >= 0 && x != 0)
+            atomicAdd(reinterpret_cast<unsigned long long*>(p.score) + s, (unsigned long long)x);
+        x = 0;
     };
     auto rebase = [&]() {                        // after sid_base / rbase / s_end changed
         const long long d = s_end - rbase;
@@ -134,8 +136,8 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
         c0 = c0_base + off;
         chi = chi_base + ((c0 < c0_base) ? (1u << 24) : 0u);   // carry into the id's bits 32..39
         ra = srow.x; rb = srow.y;
-        t = t_init; x = 0;
-        if constexpr (DET) { acc += (long long)det_w; nst += det_n; }
+        t = t_init;
+        if constexpr (DET) { x += det_w; nst += det_n; }
     };
 
     while (true) {
@@ -154,6 +156,7 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
             cur = end;
             if (!exhausted) {
                 nsteps += nst; nst = 0;
+                if (x >= 0x80000000u) flush_score();       // keeps the 32-bit running score from wrapping
                 long long a = 0;
                 if (lane == 0) a = (long long)atomicAdd(p.work_next, (unsigned long long)p.range);
                 a = __shfl_sync(NRW_FULL_MASK, a, 0);
@@ -207,7 +210,6 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
                     x -= wgt;
                     if (!absorbed) ++nsurv;
                 }
-                acc += (long long)x;
                 nst += (uint32_t)tl;
                 t = -1;
             }
