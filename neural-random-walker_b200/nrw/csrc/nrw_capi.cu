@@ -212,6 +212,11 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
     }
     p.node_hist = w->node_hist; p.count_tn = w->count_tn;
     p.t_cap = w->t_cap; p.per_start = w->count_per_start;
+    {   // warp-aggregated (match_any) or plain shared-memory atomics for the time-resolved counts:
+        // aggregation pays when walks are short and lanes share bins; NRW_CNT_MATCH=0/1 overrides
+        const char* m_env = getenv("NRW_CNT_MATCH");
+        p.cnt_match = m_env ? (strcmp(m_env, "0") != 0) : (w->t_cap <= 256);
+    }
     p.counters = w->counters; p.work_next = e->work_next;
     if (w->count_tn && w->t_cap < 1) return fail(NRW_EINVAL, "nrw_walk_philox: t_cap=%d", w->t_cap);
 

@@ -41,7 +41,7 @@ struct WalkParams {
     long long* score; double* score_sq;
     uint32_t cwpack; double cv[4]; const double* tw;
     unsigned long long* node_hist;
-    uint32_t* count_tn; int t_cap; int per_start; int cnt_bins;
+    uint32_t* count_tn; int t_cap; int per_start; int cnt_bins; int cnt_match;
     unsigned long long* counters;
     unsigned long long* work_next; long long range;
     // shared-memory carve-up (byte offsets into dynamic smem)
@@ -288,8 +288,12 @@ walk_philox_kernel(const __grid_constant__ WalkParams p) {
             if (stepped) {
                 if (t < p.t_cap) bin = (gq * p.t_cap + t) * p.n_rows + knew; else ++novf;
             }
-            const unsigned m = __match_any_sync(NRW_FULL_MASK, bin);
-            if (bin >= 0 && lane == __ffs(m) - 1) atomicAdd(cnt_s + bin, (uint32_t)__popc(m));
+            if (p.cnt_match) {       // many lanes on the same (t, node) bin (short walks): one atomic per bin
+                const unsigned m = __match_any_sync(NRW_FULL_MASK, bin);
+                if (bin >= 0 && lane == __ffs(m) - 1) atomicAdd(cnt_s + bin, (uint32_t)__popc(m));
+            } else if (bin >= 0) {   // lanes spread over many bins (long walks): plain shared-memory atomics
+                atomicAdd(cnt_s + bin, 1u);
+            }
         }
         if constexpr (TL & TL_CNT_G) {
             if (stepped) {
