@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """A/B timing of the score kernel's launch variants on a mesh (run on a B200).
-Usage: python tools/k1s_variants.py [c1|c5] [walkers_per_node]"""
+Usage: python tools/k1s_variants.py [c1|c5|c4] [walkers_per_node]"""
 import json
 import os
 import sys
@@ -18,8 +18,8 @@ def main():
     from nrw import mesh, tables
     from nrw.engine import Engine
     which = sys.argv[1] if len(sys.argv) > 1 else "c1"
-    par = dict(c1=(0.01, 1.0 / 15.0), c5=(0.01, 0.02))[which]
-    M = int(sys.argv[2]) if len(sys.argv) > 2 else dict(c1=150000, c5=12500)[which]
+    par = dict(c1=(0.01, 1.0 / 15.0), c5=(0.01, 0.02), c4=(0.001, 1.0 / 63.0))[which]
+    M = int(sys.argv[2]) if len(sys.argv) > 2 else dict(c1=150000, c5=12500, c4=200)[which]
     eng = Engine(0)
     csr = mesh.build_fluence_csr(par[0], par[1], 200, 0.15, 1)
     src = mesh.source_values(csr.meta["mesh"]["meshpoints"], mesh.source_default)
