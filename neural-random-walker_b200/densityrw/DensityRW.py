@@ -47,7 +47,7 @@ class CSRTransitions(dict):
             raise KeyError(key)
         i = int(key[0])
         lo, hi = int(self.csr.indptr[i]), int(self.csr.indptr[i + 1])
-        nb = [((int(c),), float(p)) for c, p in zip(self.csr.cols[lo:hi], self.csr.vals[lo:hi])]
+        nb = [((int(c),), float(p)) for c, p in zip(self.csr.cols[lo:hi], self.csr.vals[lo:hi]) if p > 0]
         if self.remove_sink_connections and len(nb) == 1 and nb[0] == ((i,), 1.0):
             nb = []
         return SpikingPDE.Transition(location=(i,), neighbors=nb)
@@ -63,33 +63,38 @@ def load_transitions(mat_file, remove_sink_connections=True, verbose=1):
     """DensityRW.py:177-205: matrix file -> ``{(i,): Transition}``; an entry > 0 is an edge; a node
     whose only edge is a probability-1 self-loop is a sink and, with ``remove_sink_connections``,
     loses it (walkers arriving there are counted once and stop).  ``.csv`` is parsed as the reference
-    does; ``.mat`` needs scipy; ``.npz`` (CSR, additive) returns a lazy ``CSRTransitions``."""
+    does; ``.mat`` needs scipy; ``.npz`` holds CSR (additive).  The result is a ``CSRTransitions``: a
+    dict-like ``{(i,): Transition}`` view of the parsed matrix."""
     SpikingPDE.reset_neuron_list()
-    if '.npz' in mat_file:
-        return CSRTransitions(_mesh.load_matrix(mat_file), remove_sink_connections)
-    if '.mat' in mat_file:
+    if '.npz' in mat_file or '.csv' in mat_file:
+        # parsed once per (path, mtime, size) -- the reference re-parses the CSV on every call
+        # (0.5 s for the 901 x 901 default matrix, once per start node) -- and kept as CSR; the
+        # Transition objects are built when a key is looked up
+        csr = _mesh.load_matrix(mat_file)
+        if csr.n_live != csr.n_rows:           # every row may be stepped on this surface; derived once, so
+            full = csr.meta.get("_all_live")   # that repeated calls share one set of device tables
+            if full is None:
+                full = _mesh.TransitionCSR(csr.n_rows, csr.n_rows, csr.indptr, csr.cols, csr.vals, {})
+                csr.meta["_all_live"] = full
+            csr = full
+        transitions = CSRTransitions(csr, remove_sink_connections)
+    elif '.mat' in mat_file:
         from scipy.io import loadmat
         prob_mtx = np.asarray(loadmat(mat_file)[mat_file[:-4]], dtype=np.float64)
-    elif '.csv' in mat_file:
-        prob_mtx = np.genfromtxt(mat_file, delimiter=',')
-        prob_mtx = np.atleast_2d(prob_mtx)
+        transitions = CSRTransitions(_mesh.csr_from_dense(prob_mtx, n_live=prob_mtx.shape[0]),
+                                     remove_sink_connections)
     else:
         raise ValueError("Matrix file incompatible")
-    transitions = {}
-    for i in range(prob_mtx.shape[0]):
-        row = prob_mtx[i]
-        cols = np.nonzero(row > 0)[0]
-        neighbors = [((int(j),), row[j]) for j in cols]
-        if verbose > 0:
+    if verbose > 0:
+        csr = transitions.csr
+        for i in range(csr.n_rows):
             p = 0
-            for x in row:               # sequential sum, as the reference accumulates it (:192)
+            for x in csr.vals[csr.indptr[i]:csr.indptr[i + 1]]:     # sequential sum, as the reference (:192)
                 p += x
             rw_logger.info("node " + str(i) + " has total probability of " + str(p))
-        if remove_sink_connections and len(neighbors) == 1 and neighbors[0] == ((i,), 1.0):
-            if verbose > 0:
+            nb = transitions[(i,)].neighbors
+            if remove_sink_connections and not nb and csr.indptr[i + 1] - csr.indptr[i] == 1:
                 rw_logger.info("Removing connections from a sink at " + str((i,)))
-            neighbors = []
-        transitions[(i,)] = SpikingPDE.Transition(location=(i,), neighbors=neighbors)
     return transitions
 
 
@@ -113,19 +118,23 @@ def transitions_to_csr(transitions) -> _mesh.TransitionCSR:
         csr = transitions.csr
         if not transitions.remove_sink_connections:
             return csr
+        if "_no_sinks" in csr.meta:
+            return csr.meta["_no_sinks"]
         lens = csr.row_lengths()
         rows = np.nonzero(lens == 1)[0]
         at = csr.indptr[rows]
         sinks = rows[(csr.cols[at] == rows) & (csr.vals[at] == 1.0)]
         if len(sinks) == 0:
+            csr.meta["_no_sinks"] = csr
             return csr
         keep = np.ones(csr.nnz, dtype=bool)
         keep[csr.indptr[sinks]] = False
         lens = lens.copy()
         lens[sinks] = 0
         indptr = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
-        return _mesh.TransitionCSR(csr.n_rows, csr.n_rows, indptr, csr.cols[keep], csr.vals[keep],
-                                   dict(csr.meta))
+        out = _mesh.TransitionCSR(csr.n_rows, csr.n_rows, indptr, csr.cols[keep], csr.vals[keep], {})
+        csr.meta["_no_sinks"] = out
+        return out
     if isinstance(transitions, _mesh.TransitionCSR):
         return transitions
     keys = sorted(transitions.keys())
