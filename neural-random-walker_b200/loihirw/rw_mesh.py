@@ -31,8 +31,11 @@ def load_mesh(custom_network, n_live=None):
         return _mesh.csr_from_dense(q, n_live=q.shape[0] if n_live is None else n_live)
     csr = _mesh.load_matrix(custom_network)
     want = csr.n_rows if n_live is None else int(n_live)
-    if csr.n_live != want:
-        csr = _mesh.TransitionCSR(csr.n_rows, want, csr.indptr, csr.cols, csr.vals, dict(csr.meta))
+    if csr.n_live != want:                      # derived once per file: repeated calls share device tables
+        key = "_n_live_%d" % want
+        if key not in csr.meta:
+            csr.meta[key] = _mesh.TransitionCSR(csr.n_rows, want, csr.indptr, csr.cols, csr.vals, {})
+        csr = csr.meta[key]
     return csr
 
 

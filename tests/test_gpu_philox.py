@@ -418,3 +418,59 @@ def test_deterministic_rows_on_a_general_graph(engine, k1_env):
                 res = engine.walk(tabs, starts, counts, nt, 31, score=True, class_value=cv)
                 port = philox_port.walk_port(csr, starts, counts, nt, 31, alias=tabs.alias_host, class_value=cv)
                 _cmp(res, port, hist=False)
+
+
+@pytest.mark.parametrize("seed", list(range(8)))
+def test_random_graphs_differential(engine, k1_env, seed):
+    """Differential test on random sparse graphs: both kernels == numpy port for random row lengths,
+    absorbing rows anywhere, single-successor rows (absorbing and live targets, self loops), random
+    classes / weights, ragged start lists, id windows and stream-id bases."""
+    from nrw import mesh
+    from oracle import philox_port
+    rng = np.random.default_rng(1000 + seed)
+    n = int(rng.integers(5, 200))
+    q = np.zeros((n, n))
+    for i in range(n):
+        kind = rng.random()
+        if kind < 0.15:
+            continue                                           # absorbing row
+        if kind < 0.35:
+            q[i, rng.integers(0, n)] = 1.0                     # single successor (maybe itself)
+            continue
+        k = int(rng.integers(2, min(n, 12) + 1))
+        cols = rng.choice(n, size=k, replace=False)
+        q[i, cols] = rng.dirichlet(np.ones(k) * rng.choice([0.3, 1.0, 5.0]))
+    n_live = int(rng.integers(max(n // 2, 1), n + 1))
+    csr = mesh.csr_from_dense(q, n_live=n_live)
+    nc = rng.integers(0, 4, size=n).astype(np.uint8)
+    tabs = engine.upload(csr, node_class=nc)
+    n_starts = int(rng.integers(1, 12))
+    starts = rng.integers(0, n, size=n_starts)
+    counts = rng.integers(0, 3000, size=n_starts)
+    counts[rng.random(n_starts) < 0.2] = 0
+    total = int(counts.sum())
+    if total == 0:
+        counts[0] = total = 50
+    cv = [0, 1, 2, 3] if rng.random() < 0.5 else [int(x) for x in rng.integers(0, 256, size=4)]
+    nt = int(rng.integers(2, 50))
+    lo = int(rng.integers(0, total))
+    window = None if rng.random() < 0.5 else (lo, int(rng.integers(lo, total + 1)))
+    idb = None if rng.random() < 0.5 else rng.integers(0, 2 ** 39, size=n_starts)
+    port = philox_port.walk_port(csr, starts, counts, nt, seed, alias=tabs.alias_host, class_value=cv,
+                                 walker_range=window, start_id_base=idb)
+    for variant in ("fast", "fast_nodet", "general"):
+        k1_env(variant)
+        res = engine.walk(tabs, starts, counts, nt, seed, score=True, class_value=cv, walker_range=window,
+                          start_id_base=idb)
+        _cmp(res, port, hist=False)
+
+
+def test_microbench_rates_are_sane(engine):
+    """nrw_microbench: the roofline denominators bench.py reports (operations per second)."""
+    for kind, n, iters in (("smem_load", 20000, 200), ("smem_atomic", 10001, 200), ("l2_load", 158761, 200),
+                           ("global_atomic", 10001, 50)):
+        rate = engine.microbench(kind, n, iters=iters, reps=2)
+        assert 1e9 < rate < 1e14, (kind, rate)
+    from nrw.engine import NrwError
+    with pytest.raises(NrwError):
+        engine.microbench("smem_load", 10 ** 6)                  # 8 MB does not fit shared memory
