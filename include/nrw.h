@@ -100,7 +100,7 @@ typedef struct nrw_walk {
      * when start_id_base is NULL.  Lets a rank walk a slice of EVERY start's walkers while
      * each walker keeps the stream it has in the unsharded run.  ids must be < 2^40.    */
     const int64_t* start_id_base;   /* [n_starts] or NULL                                */
-    uint64_t seed;                  /* Philox key = hash(seed); counter = (stream id, step) */
+    uint64_t seed;                  /* Philox key = hash(seed); counter = (stream id, step), or (stream id, step pair) on COMPACT tables: csrc/common.cuh */
     int32_t  nt;                    /* neuraltime: model steps t = 1 .. nt-1 (:236)      */
     int32_t  sampler;               /* NRW_SAMPLER_*                                     */
 

@@ -1,10 +1,18 @@
 // common.cuh -- shared device helpers for libnrw (sm_100a only).
 //
 // Philox2x32-10 (Salmon et al., "Parallel random numbers: as easy as 1, 2, 3", SC'11) is the
-// counter-based generator behind the on-device walk: one call per walker-step, counter =
-// (walker id, step), key = hash(seed).  It replaces the reference's single sequential
-// MT19937 stream (fluence_mini_app.py:243, :523) in the statistical ("philox") mode; the
-// bit-exact mode consumes the reference's own stream instead (walk_replay.cuh).
+// counter-based generator behind the on-device walk, key = hash(seed).  It replaces the reference's
+// single sequential MT19937 stream (fluence_mini_app.py:243, :523) in the statistical ("philox")
+// mode; the bit-exact mode consumes the reference's own stream instead (walk_replay.cuh).
+//
+// Draw of walker `id` for model step t (1-based), by table layout:
+//   * WIDE alias tables and the CDF search: one call per step, counter (id, t); the alias slot comes
+//     from word 0, the coin from word 1; the CDF search uses both as one 53-bit uniform.
+//   * COMPACT alias tables ("paired draws"): one call per PAIR of steps, counter (id, (t-1)|1); step
+//     t uses word 0 when t is odd, word 1 when even.  The word w and the row length n give
+//     v = w * n (64 bit): slot = v >> 32, coin = v & 0xffffffff, primary target iff coin <= threshold.
+//     Rows have n <= 1023 entries, so slot and coin deviate from exact uniformity by < n / 2^32
+//     (2.4e-7 relative at worst, 2e-9 on a 9-point stencil) -- far below any Monte-Carlo error reachable.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -29,6 +37,11 @@ __device__ __forceinline__ uint2 philox2x32_10(uint32_t c0, uint32_t c1, uint32_
     }
     return make_uint2(c0, c1);
 }
+
+// counter word 1 of the call that serves model step t (t >= 1, < 2^24) under the paired scheme, and the
+// word of its result that step t uses
+__host__ __device__ __forceinline__ uint32_t pair_counter(uint32_t t) { return (t - 1u) | 1u; }
+__host__ __device__ __forceinline__ uint32_t pair_word(uint2 r, uint32_t t) { return (t & 1u) ? r.x : r.y; }
 
 // 64-bit seed -> 32-bit Philox key (host mirror: nrw/philox.py::seed_to_key).
 __host__ __device__ __forceinline__ uint32_t seed_to_key(uint64_t seed) {

@@ -7,7 +7,8 @@
 //     lanes; no atomics), so lanes stay busy although the mean walk is only ~2 steps long;
 //   * warps pull contiguous walker-id ranges from one global counter (dynamic balance, one
 //     atomic per `range` walkers);
-//   * Philox2x32-10 keyed by the seed with counter (walker id, step): any walker's trajectory is
+//   * Philox2x32-10 keyed by the seed with counter (walker id, step) -- (walker id, step pair) on
+//     compact tables, see common.cuh: any walker's trajectory is
 //     a pure function of (seed, id), independent of grid shape and of how ranks shard the ids;
 //   * transition tables: de-duplicated alias patterns + per-row descriptors staged ONCE per CTA
 //     into shared memory with 1-D TMA bulk copies (UBLKCP) when they fit (TAB_SMEM), descriptors
@@ -243,7 +244,8 @@ walk_philox_kernel(const __grid_constant__ WalkParams p) {
         int knew = 0;
         if (stepped) {
             ++t; ++nsteps;
-            const uint2 r = philox2x32_10(c0, chi | (uint32_t)t, key);
+            constexpr bool PAIRED = (TAB == TAB_SMEM || TAB == TAB_HYB);     // compact tables: paired draws
+            const uint2 r = philox2x32_10(c0, chi | (PAIRED ? pair_counter((uint32_t)t) : (uint32_t)t), key);
             if constexpr (TAB == TAB_CDF) {
                 knew = sample_cdf(p.indptr, p.cols, p.cum, (int)row.a, u53(r.x, r.y));
             } else if constexpr (TAB == TAB_GLB) {
@@ -252,9 +254,9 @@ walk_philox_kernel(const __grid_constant__ WalkParams p) {
                 knew = (int)(row.c + ((r.y <= e.x) ? e.y : e.z));
             } else {
                 const uint32_t n = row_len(row.a), off = row_off(row.a);
-                const uint32_t slot = __umulhi(r.x, n);
-                const uint2 e = alias_s[off + slot];
-                knew = (int)(row.b + ((r.y <= e.x) ? (e.y & 0xffffu) : (e.y >> 16)));
+                const unsigned long long v = (unsigned long long)pair_word(r, (uint32_t)t) * n;
+                const uint2 e = alias_s[off + (uint32_t)(v >> 32)];
+                knew = (int)(row.b + (((uint32_t)v <= e.x) ? (e.y & 0xffffu) : (e.y >> 16)));
             }
             row = load_row<TAB>(p, rowinfo_s, knew);
         }

@@ -147,6 +147,19 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
         const uint32_t off = cur + (uint32_t)__popc(need & lt_mask);
         const uint32_t ncur = cur + (uint32_t)__popc(need);
         if (ncur <= end) {
+            if constexpr (DET) {
+                // the whole warp is idle inside a deterministic-exit start (nothing there ever enters the
+                // step phase): account for every id the range and the start still hold in one go, lane L
+                // standing for ids cur + L, cur + L + 32, ...
+                if (need == NRW_FULL_MASK && __all_sync(NRW_FULL_MASK, det_n != 0u && off < s_end_off)) {
+                    const uint32_t lim = min(end, s_end_off);
+                    const uint32_t k = (lim - cur - (uint32_t)lane + 31u) >> 5;
+                    x += det_w * k;
+                    nst += k;
+                    cur = lim;
+                    continue;
+                }
+            }
             cur = ncur;
             if (dead) take(off);
         } else {
@@ -179,12 +192,11 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
         __syncwarp();
 
         // ---- one model step (fluence_mini_app.py:243-245 + the fused :428-434) -----------------------
-        if (t >= 0) {
+        auto step = [&](uint32_t slot, uint32_t coin) {
             const int tn = t + 1;
-            const uint2 r = philox2x32_10_rk(c0, chi | (uint32_t)tn, p);
-            const uint32_t n = row_len(ra), aoff = row_off(ra);
-            const uint2 e = alias_s[aoff + __umulhi(r.x, n)];
-            const int knew = (int)(rb + ((r.y <= e.x) ? (e.y & 0xffffu) : (e.y >> 16)));
+            const uint32_t aoff = row_off(ra);
+            const uint2 e = alias_s[aoff + slot];
+            const int knew = (int)(rb + ((coin <= e.x) ? (e.y & 0xffffu) : (e.y >> 16)));
             const uint2 row = load_row2<TAB>(p, rowinfo_s, knew);
             ra = row.x; rb = row.y;
             uint32_t wgt = IDW ? (row.x >> 30) : ((p.cwpack >> ((row.x >> 27) & 0x18u)) & 0xffu);
@@ -212,6 +224,17 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
                 }
                 nst += (uint32_t)tl;
                 t = -1;
+            }
+        };
+        // one Philox call serves the two steps of a pair (common.cuh, "paired draws"): lanes are refilled
+        // only here, so every live lane is at an even t and the whole warp shares the call
+        if (t >= 0) {
+            const uint2 r = philox2x32_10_rk(c0, chi | (uint32_t)(t + 1), p);
+            const unsigned long long va = (unsigned long long)r.x * row_len(ra);
+            step((uint32_t)(va >> 32), (uint32_t)va);
+            if (t >= 0) {
+                const unsigned long long vb = (unsigned long long)r.y * row_len(ra);
+                step((uint32_t)(vb >> 32), (uint32_t)vb);
             }
         }
     }

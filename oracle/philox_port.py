@@ -103,9 +103,14 @@ def walk_port(csr, start_nodes, start_counts, nt, seed, *, alias=None, cum=None,
         if len(idx) == 0:
             break
         steps += len(idx)
-        r0, r1 = philox2x32_10(c0[idx], chi[idx] | np.uint32(t), key)
+        paired = sampler == "alias" and alias.layout == "compact"      # common.cuh: "paired draws"
+        r0, r1 = philox2x32_10(c0[idx], chi[idx] | np.uint32(((t - 1) | 1) if paired else t), key)
         kk = k[idx]
-        if sampler == "alias":
+        if paired:
+            v = (r0 if (t & 1) else r1).astype(np.uint64) * nrow[kk].astype(np.uint64)
+            e = off[kk] + (v >> np.uint64(32)).astype(np.int64)
+            knew = base[kk] + np.where((v & MASK).astype(np.uint32) <= th[e], aa[e], bb[e])
+        elif sampler == "alias":
             slot = ((r0.astype(np.uint64) * nrow[kk].astype(np.uint64)) >> np.uint64(32)).astype(np.int64)
             e = off[kk] + slot
             knew = base[kk] + np.where(r1 <= th[e], aa[e], bb[e])
