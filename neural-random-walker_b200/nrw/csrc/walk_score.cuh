@@ -92,15 +92,32 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
             atomicAdd(reinterpret_cast<unsigned long long*>(p.score) + s, (unsigned long long)x);
         x = 0;
     };
-    auto rebase = [&]() {                        // after sid_base / rbase / s_end changed
+    // after sid_base / rbase / s_end changed.  s_end_off is the first range offset the hot path may not
+    // take with the lane's current bases: the end of the start node, or the offset at which the low word
+    // of the stream id wraps (the take then goes through next_start, which carries into bits 32..39).
+    auto rebase = [&]() {
         const long long d = s_end - rbase;
         s_end_off = d <= 0 ? 0u : (d > 0x7fffffffll ? 0x7fffffffu : (uint32_t)d);
         c0_base = (uint32_t)sid_base;
         chi_base = (uint32_t)((unsigned long long)sid_base >> 32) << 24;
+        const uint32_t wrap_off = 0u - c0_base;              // c0_base + wrap_off == 2^32 (0: no wrap ahead)
+        if (wrap_off != 0u && wrap_off < s_end_off) s_end_off = wrap_off;
+    };
+    auto pass_wrap = [&]() {
+        chi_base += 1u << 24;
+        const long long d = s_end - rbase;
+        s_end_off = d > 0x7fffffffll ? 0x7fffffffu : (uint32_t)d;
     };
     // cold: the id at range offset `off` belongs to a later start than the lane's current one
     auto next_start = [&](uint32_t off) {
         const long long gnew = rbase + (long long)off;
+        if (s >= 0 && gnew < s_end) {
+            // same start: the low word of the stream id wraps at or before `off` (rebase() clamped
+            // s_end_off there).  c0_base + off wraps by itself; carry into bits 32..39 and restore the
+            // start's real end (a range is far shorter than 2^32: no second wrap before the next rebase)
+            pass_wrap();
+            return;
+        }
         flush_score();
         long long s_lo = s_end;
         bool found = false;
@@ -121,6 +138,7 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
         srow = load_row2<TAB>(p, rowinfo_s, __ldg(p.start_nodes + s));
         sid_base = rbase + (p.start_id_base ? (__ldg(p.start_id_base + s) - s_lo) : 0ll);
         rebase();
+        if (off >= s_end_off) pass_wrap();       // the new start's ids wrapped before this lane's first one
         t_init = ((srow.x & ROW_N_MASK) == 0u) ? -1 : 0;       // started on the sink: an exit, no step
         if constexpr (DET) {
             // a start whose single successor is absorbing: every walker takes that one step (t = 1)
@@ -134,7 +152,7 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
     auto take = [&](uint32_t off) {
         if (off >= s_end_off) [[unlikely]] next_start(off);
         c0 = c0_base + off;
-        chi = chi_base + ((c0 < c0_base) ? (1u << 24) : 0u);   // carry into the id's bits 32..39
+        chi = chi_base;
         ra = srow.x; rb = srow.y;
         t = t_init;
         if constexpr (DET) { x += det_w; nst += det_n; }
@@ -199,30 +217,38 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
             const int knew = (int)(rb + ((coin <= e.x) ? (e.y & 0xffffu) : (e.y >> 16)));
             const uint2 row = load_row2<TAB>(p, rowinfo_s, knew);
             ra = row.x; rb = row.y;
-            uint32_t wgt = IDW ? (row.x >> 30) : ((p.cwpack >> ((row.x >> 27) & 0x18u)) & 0xffu);
-            x += wgt;
+            x += IDW ? (row.x >> 30) : ((p.cwpack >> ((row.x >> 27) & 0x18u)) & 0xffu);
             t = tn;
             // the walk ends here when the row is absorbing, when (DET) its single successor is, or at
             // the last model step
             const bool terminal = (row.x & (DET ? ROW_TERM : ROW_N_MASK)) == (DET ? ROW_TERM : 0u);
             if (terminal || tn >= t_last) {
-                int tl = tn;
-                bool absorbed = (row.x & ROW_N_MASK) == 0u;
-                if constexpr (DET) {
-                    // single absorbing successor (fluence exit rows, fluence_mini_app.py:355-357): take
-                    // that step now -- no draw could change it
-                    if (!absorbed && tn < t_last) {
-                        wgt = weight_of(row_detcls(row.x));
-                        x += wgt;
-                        tl = tn + 1;
-                        absorbed = true;
+                if (tn + 1 < t_last) [[likely]] {
+                    // an absorbing row, or (DET) a row whose single successor is absorbing (fluence exit
+                    // rows, fluence_mini_app.py:355-357): that step is taken now -- no draw could change it
+                    if constexpr (DET) {
+                        if (row.x & ROW_DETABS) { x += weight_of(row_detcls(row.x)); ++nst; }
                     }
+                    nst += (uint32_t)tn;
+                } else {
+                    // within one step of the end of time: step nt-1 is outside the sum (:428, Q3)
+                    int tl = tn;
+                    bool absorbed = (row.x & ROW_N_MASK) == 0u;
+                    uint32_t wl = weight_of(row_class(row.x));
+                    if constexpr (DET) {
+                        if (!absorbed && tn < t_last) {
+                            wl = weight_of(row_detcls(row.x));
+                            x += wl;
+                            tl = tn + 1;
+                            absorbed = true;
+                        }
+                    }
+                    if (tl >= t_last) {
+                        x -= wl;
+                        if (!absorbed) ++nsurv;
+                    }
+                    nst += (uint32_t)tl;
                 }
-                if (tl >= t_last) [[unlikely]] {  // step nt-1 is outside the sum (:428, Q3)
-                    x -= wgt;
-                    if (!absorbed) ++nsurv;
-                }
-                nst += (uint32_t)tl;
                 t = -1;
             }
         };
