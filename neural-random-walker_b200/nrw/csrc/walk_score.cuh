@@ -226,7 +226,11 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
                 if (tn + 1 < t_last) [[likely]] {
                     // an absorbing row, or (DET) a row whose single successor is absorbing (fluence exit
                     // rows, fluence_mini_app.py:355-357): that step is taken now -- no draw could change it
-                    if constexpr (DET) {
+                    // (detcls is 0 on every row that is not such an exit row)
+                    if constexpr (DET && IDW) {
+                        x += row_detcls(row.x);
+                        nst += (row.x >> 27) & 1u;
+                    } else if constexpr (DET) {
                         if (row.x & ROW_DETABS) { x += weight_of(row_detcls(row.x)); ++nst; }
                     }
                     nst += (uint32_t)tn;
