@@ -336,8 +336,11 @@ def run_ours(args):
                     "frac": achieved / peak, "traffic": traffic, "kernel": res.kernel,
                     "kernel_ms": kernel_ms, "walker_steps_per_launch": steps_per_launch,
                     "algorithmic_bytes_per_walker_step": b_step, "peak_source": peak_src,
-                    "binding_resource": {"what": "SM issue slots (integer ALU + IMAD pipes), not memory",
+                    "binding_resource": {"what": "SM integer math issue (ALU + FMA-heavy/IMAD pipes share the "
+                                                 "half-rate dispatch; their busy cycles add up to ~100 %), not memory",
                                          "issue_slot_utilisation_ncu": ncu_facts.get("issue_active_pct"),
+                                         "alu_pipe_pct_ncu": ncu_facts.get("alu_pipe_pct"),
+                                         "fmaheavy_pipe_pct_ncu": ncu_facts.get("fmaheavy_pipe_pct"),
                                          "warp_instructions_per_walker_step_ncu": ncu_facts.get("warp_inst_per_32_walker_steps"),
                                          "source": ncu_facts.get("source")},
                     "deterministic_step_fraction": det_frac,
@@ -346,7 +349,8 @@ def run_ours(args):
                             "walker state in registers, so HBM is not the binding resource and frac > 1 "
                             "-- DESIGN.md section 3 gives the issue-slot accounting.  Steps from rows with "
                             "a single absorbing successor (deterministic_step_fraction) are taken without "
-                            "computing a draw; results are bit-identical to always drawing (ablation)."}
+                            "computing a draw; results are bit-identical to always drawing (ablation).  On "
+                            "compact tables one Philox2x32-10 call serves two steps (common.cuh)."}
         line = {"metric": METRIC, "value": value, "unit": METRIC, "n_gpus": world, "steps": args.steps,
                 "warmup": max(args.warmup, 3), "ms_per_step": total_ms / args.steps,
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32/f64",
