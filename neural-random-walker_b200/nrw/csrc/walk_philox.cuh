@@ -239,85 +239,96 @@ walk_philox_kernel(const __grid_constant__ WalkParams p) {
             }
         }
 
-        // ---- one model step for every live lane ---------------------------------------------
-        const bool stepped = t >= 0;
-        int knew = 0;
-        if (stepped) {
-            ++t; ++nsteps;
-            constexpr bool PAIRED = (TAB == TAB_SMEM || TAB == TAB_HYB);     // compact tables: paired draws
-            const uint2 r = philox2x32_10(c0, chi | (PAIRED ? pair_counter((uint32_t)t) : (uint32_t)t), key);
-            if constexpr (TAB == TAB_CDF) {
-                knew = sample_cdf(p.indptr, p.cols, p.cum, (int)row.a, u53(r.x, r.y));
-            } else if constexpr (TAB == TAB_GLB) {
-                const uint32_t slot = __umulhi(r.x, row.b);
-                const uint4 e = __ldg(reinterpret_cast<const uint4*>(p.alias) + row.a + slot);
-                knew = (int)(row.c + ((r.y <= e.x) ? e.y : e.z));
-            } else {
-                const uint32_t n = row_len(row.a), off = row_off(row.a);
-                const unsigned long long v = (unsigned long long)pair_word(r, (uint32_t)t) * n;
-                const uint2 e = alias_s[off + (uint32_t)(v >> 32)];
-                knew = (int)(row.b + (((uint32_t)v <= e.x) ? (e.y & 0xffffu) : (e.y >> 16)));
-            }
-            row = load_row<TAB>(p, rowinfo_s, knew);
+        // ---- model steps for every live lane ------------------------------------------------------
+        // compact tables: one Philox call serves a PAIR of steps (common.cuh, "paired draws"); lanes are
+        // only refilled above, so every live lane is at an even t here and the warp shares the call
+        constexpr bool PAIRED = (TAB == TAB_SMEM || TAB == TAB_HYB);
+        uint2 rp = make_uint2(0u, 0u);
+        if constexpr (PAIRED) {
+            if (t >= 0) rp = philox2x32_10(c0, chi | (uint32_t)(t + 1), key);
         }
-        const bool in_sum = stepped && (t <= t_score_max);
-
-        // ---- tallies --------------------------------------------------------------------------------
-        if constexpr (TL & TL_SCORE) {
-            if (in_sum) {
-                const uint32_t cls = row_cls<TAB>(row);
-                if constexpr (TL & TL_TW) {
-                    const double cvv = cls == 0 ? p.cv[0] : cls == 1 ? p.cv[1] : cls == 2 ? p.cv[2] : p.cv[3];
-                    x += __double2ll_rn(__ldg(p.tw + t) * cvv);
+        auto model_step = [&](const bool first) {
+            const bool stepped = t >= 0;
+            int knew = 0;
+            if (stepped) {
+                ++t; ++nsteps;
+                uint2 r = rp;
+                if constexpr (!PAIRED) r = philox2x32_10(c0, chi | (uint32_t)t, key);
+                if constexpr (TAB == TAB_CDF) {
+                    knew = sample_cdf(p.indptr, p.cols, p.cum, (int)row.a, u53(r.x, r.y));
+                } else if constexpr (TAB == TAB_GLB) {
+                    const uint32_t slot = __umulhi(r.x, row.b);
+                    const uint4 e = __ldg(reinterpret_cast<const uint4*>(p.alias) + row.a + slot);
+                    knew = (int)(row.c + ((r.y <= e.x) ? e.y : e.z));
                 } else {
-                    x += (p.cwpack >> (cls * 8u)) & 0xffu;        // byte-packed integer class weights
+                    const uint32_t n = row_len(row.a), off = row_off(row.a);
+                    const unsigned long long v = (unsigned long long)(first ? r.x : r.y) * n;
+                    const uint2 e = alias_s[off + (uint32_t)(v >> 32)];
+                    knew = (int)(row.b + (((uint32_t)v <= e.x) ? (e.y & 0xffffu) : (e.y >> 16)));
                 }
+                row = load_row<TAB>(p, rowinfo_s, knew);
             }
-        }
-        if constexpr (TL & (TL_HIST_S | TL_HIST_G)) {
-            // sink exits are the one hot bin: aggregate them with a warp vote
-            const bool hot = in_sum && (knew == p.n_rows - 1);
-            const unsigned hm = __ballot_sync(NRW_FULL_MASK, hot);
-            if (lane == 0) sinkc += __popc(hm);
-            if (in_sum && !hot) {
-                if constexpr (TL & TL_HIST_S) atomicAdd(hist_s + knew, 1u);
-                else atomicAdd(p.node_hist + knew, 1ull);
-            }
-        }
-        if constexpr (TL & TL_CNT_S) {
-            const int gq = p.per_start ? s : 0;
-            int bin = -1;
-            if (stepped) {
-                if (t < p.t_cap) bin = (gq * p.t_cap + t) * p.n_rows + knew; else ++novf;
-            }
-            if (p.cnt_match) {       // many lanes on the same (t, node) bin (short walks): one atomic per bin
-                const unsigned m = __match_any_sync(NRW_FULL_MASK, bin);
-                if (bin >= 0 && lane == __ffs(m) - 1) atomicAdd(cnt_s + bin, (uint32_t)__popc(m));
-            } else if (bin >= 0) {   // lanes spread over many bins (long walks): plain shared-memory atomics
-                atomicAdd(cnt_s + bin, 1u);
-            }
-        }
-        if constexpr (TL & TL_CNT_G) {
-            if (stepped) {
-                const long long gq = p.per_start ? s : 0;
-                if (t < p.t_cap)
-                    atomicAdd(p.count_tn + ((size_t)(gq * p.t_cap + t) * (size_t)p.n_rows + (size_t)knew), 1u);
-                else ++novf;
-            }
-        }
+            const bool in_sum = stepped && (t <= t_score_max);
 
-        // ---- absorption / sink exit / end of time ------------------------------------------------
-        if (stepped) {
-            const bool absorbed = row_n<TAB>(row) == 0u;
-            if (absorbed || t >= t_last) {
-                if (!absorbed) ++nsurv;
-                t = -1;
-                if constexpr (TL & TL_SCORE) {
-                    acc += (long long)x;
-                    if (p.score_sq) { const double xd = (double)x; acc2 += xd * xd; }
+            // ---- tallies --------------------------------------------------------------------------------
+            if constexpr (TL & TL_SCORE) {
+                if (in_sum) {
+                    const uint32_t cls = row_cls<TAB>(row);
+                    if constexpr (TL & TL_TW) {
+                        const double cvv = cls == 0 ? p.cv[0] : cls == 1 ? p.cv[1] : cls == 2 ? p.cv[2] : p.cv[3];
+                        x += __double2ll_rn(__ldg(p.tw + t) * cvv);
+                    } else {
+                        x += (p.cwpack >> (cls * 8u)) & 0xffu;        // byte-packed integer class weights
+                    }
                 }
             }
-        }
+            if constexpr (TL & (TL_HIST_S | TL_HIST_G)) {
+                // sink exits are the one hot bin: aggregate them with a warp vote
+                const bool hot = in_sum && (knew == p.n_rows - 1);
+                const unsigned hm = __ballot_sync(NRW_FULL_MASK, hot);
+                if (lane == 0) sinkc += __popc(hm);
+                if (in_sum && !hot) {
+                    if constexpr (TL & TL_HIST_S) atomicAdd(hist_s + knew, 1u);
+                    else atomicAdd(p.node_hist + knew, 1ull);
+                }
+            }
+            if constexpr (TL & TL_CNT_S) {
+                const int gq = p.per_start ? s : 0;
+                int bin = -1;
+                if (stepped) {
+                    if (t < p.t_cap) bin = (gq * p.t_cap + t) * p.n_rows + knew; else ++novf;
+                }
+                if (p.cnt_match) {       // many lanes on the same (t, node) bin (short walks): one atomic per bin
+                    const unsigned m = __match_any_sync(NRW_FULL_MASK, bin);
+                    if (bin >= 0 && lane == __ffs(m) - 1) atomicAdd(cnt_s + bin, (uint32_t)__popc(m));
+                } else if (bin >= 0) {   // lanes spread over many bins (long walks): plain shared-memory atomics
+                    atomicAdd(cnt_s + bin, 1u);
+                }
+            }
+            if constexpr (TL & TL_CNT_G) {
+                if (stepped) {
+                    const long long gq = p.per_start ? s : 0;
+                    if (t < p.t_cap)
+                        atomicAdd(p.count_tn + ((size_t)(gq * p.t_cap + t) * (size_t)p.n_rows + (size_t)knew), 1u);
+                    else ++novf;
+                }
+            }
+
+            // ---- absorption / sink exit / end of time ------------------------------------------------
+            if (stepped) {
+                const bool absorbed = row_n<TAB>(row) == 0u;
+                if (absorbed || t >= t_last) {
+                    if (!absorbed) ++nsurv;
+                    t = -1;
+                    if constexpr (TL & TL_SCORE) {
+                        acc += (long long)x;
+                        if (p.score_sq) { const double xd = (double)x; acc2 += xd * xd; }
+                    }
+                }
+            }
+            };
+        model_step(true);
+        if constexpr (PAIRED) model_step(false);
     }
 
     // ---- epilogue: flush register tallies, merge the CTA histogram once ----------------------
