@@ -7,19 +7,23 @@
 //   * refill with ONE vote per iteration: dead lanes rank themselves with popc and take consecutive
 //     ids; everything rare (range exhausted, next start node, 2^32 carry of the stream id, walkers on
 //     absorbing starts) sits behind warp-uniform or [[unlikely]] branches;
+//   * paired draws (common.cuh): a refill is followed by TWO steps sharing one Philox call -- lanes
+//     are only refilled at the top of the pair, so every live lane is at an even step;
 //   * the Philox round keys come from the kernel parameters (constant-bank operands), not from
 //     uniform-register arithmetic repeated every iteration;
 //   * the score is a per-lane running sum over the lane's walkers (flushed when the start node
 //     changes and at every range fetch), added to unconditionally each step; the step t = nt-1
-//     (outside the solution sum, fluence_mini_app.py:428) is taken back out on the rare end-of-time
-//     path; walker-steps are accumulated as lifetimes at death instead of once per step;
-//   * IDW: class weights equal to the class index turn the weight lookup into one LEA.HI;
+//     (outside the solution sum, fluence_mini_app.py:428) is dealt with on the rare path of walks
+//     ending within one step of the end of time; walker-steps are accumulated as lifetimes at death
+//     instead of once per step;
+//   * IDW: class weights equal to the class index need no weight lookup;
 //   * DET: a row whose single successor is absorbing (every exit row of the fluence mesh: 45 % of
 //     all walker-steps) is stepped without computing a draw -- slot 0 with threshold 2^32-1 is taken
 //     whatever the draw is, so tallies and counters stay bit-identical to the always-draw port.  A
 //     walker landing on such a row takes its exit step in the same iteration; walkers STARTING on
-//     one are accounted for by the refill (one step, one tally, exit) and never enter the step phase,
-//     so warps inside such a start node skip the step phase altogether.  NRW_DET=0 disables it.
+//     one never enter the step phase: an idle warp inside such a start accounts for all the ids the
+//     range and the start still hold at once (one step, one tally, one exit each), lanes that pick
+//     them up one by one account for them in the take.  NRW_DET=0 disables it.
 // Requires nt >= 2 (the planner sends nt = 1 to the general kernel).
 #pragma once
 #include "walk_philox.cuh"

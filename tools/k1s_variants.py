@@ -27,9 +27,9 @@ def main():
     tabs = eng.upload(csr, node_class=nc)
     starts = np.arange(csr.n_live)
     flush = torch.empty(512 << 20, dtype=torch.uint8, device=eng.device)
-    for tag, env in (("default", {}), ("pair", {"NRW_PAIR": "1"}), ("pair_cps1", {"NRW_PAIR": "1", "NRW_CPS": "1"}), ("cps1", {"NRW_CPS": "1"}), ("always_draw", {"NRW_DET": "0"}),
+    for tag, env in (("default", {}), ("cps1", {"NRW_CPS": "1"}), ("always_draw", {"NRW_DET": "0"}),
                      ("general", {"NRW_K1": "general"})):
-        for k in ("NRW_CPS", "NRW_DET", "NRW_K1", "NRW_PAIR"):
+        for k in ("NRW_CPS", "NRW_DET", "NRW_K1"):
             os.environ.pop(k, None)
         os.environ.update(env)
         launch, res = eng.prepare_walk(tabs, starts, M, 30000, seed=1, score=True, class_value=[0, 1, 0, 0])
