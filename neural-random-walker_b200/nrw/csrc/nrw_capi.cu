@@ -439,11 +439,11 @@ extern "C" int nrw_fluence_scores_host(nrw_engine* e, int32_t n_rows, int32_t n_
     w.sampler = NRW_SAMPLER_ALIAS; w.score = (int64_t*)e->d_score;
     {   // weights of classes no row carries are free: if the used ones equal the class index, pass the
         // identity vector so that the walk takes the IDW kernel (walk_score.cuh)
-        uint32_t max_cls = 0;
+        uint32_t present = 0;
         const uint32_t* ri = (const uint32_t*)rowinfo_host;
-        for (int32_t r = 0; r < n_rows; ++r) { const uint32_t c = ri[2 * r] >> 30; if (c > max_cls) max_cls = c; }
+        for (int32_t r = 0; r < n_rows; ++r) present |= 1u << (ri[2 * r] >> 30);
         bool ident = true;
-        for (uint32_t c = 0; c <= max_cls; ++c) ident = ident && class_value[c] == (double)c;
+        for (uint32_t c = 0; c < 4; ++c) if ((present >> c) & 1u) ident = ident && class_value[c] == (double)c;
         for (int i = 0; i < 4; ++i) w.class_value[i] = ident ? (double)i : class_value[i];
     }
     w.counters = e->d_counters;

@@ -507,15 +507,30 @@ class Engine:
     def fluence_scores_host(self, alias_tables, n_rows, n_live, start_nodes, start_prefix, walker_lo,
                             walker_hi, seed, nt, class_value, score_out, counters_out):
         """nrw_fluence_scores_host: numpy (ideally pinned) buffers in, numpy buffers out, synchronous."""
+        self.prepare_fluence_scores_host(alias_tables, n_rows, n_live, start_nodes, start_prefix, walker_lo,
+                                         walker_hi, nt, class_value, score_out, counters_out)(seed)
+
+    def prepare_fluence_scores_host(self, alias_tables, n_rows, n_live, start_nodes, start_prefix, walker_lo,
+                                    walker_hi, nt, class_value, score_out, counters_out):
+        """The same call with its arguments converted once: returns ``solve(seed)`` for a loop of solves
+        over the same buffers (a CUDA-graph replay of the copy / walk / copy-back sequence was measured
+        and gave nothing: the per-call cost beyond the kernel, ~50 us, is DMA and synchronisation latency)."""
         if alias_tables.layout != "compact":
             raise NrwError("the host entry takes the compact alias layout")
         cv = (C.c_double * 4)(*[float(x) for x in class_value])
-        self._check(self.lib.nrw_fluence_scores_host(
-            self.handle, int(n_rows), int(n_live), alias_tables.n_alias,
-            C.c_void_p(alias_tables.rowinfo.ctypes.data), C.c_void_p(alias_tables.alias.ctypes.data),
-            len(start_nodes), C.c_void_p(start_nodes.ctypes.data), C.c_void_p(start_prefix.ctypes.data),
-            int(walker_lo), int(walker_hi), int(seed) & 0xFFFFFFFFFFFFFFFF, int(nt), C.byref(cv),
-            C.c_void_p(score_out.ctypes.data), C.c_void_p(counters_out.ctypes.data), self.stream))
+        keep = (alias_tables.rowinfo, alias_tables.alias, start_nodes, start_prefix, score_out, counters_out, cv)
+        fn, check, handle, stream = self.lib.nrw_fluence_scores_host, self._check, self.handle, self.stream
+        head = (handle, int(n_rows), int(n_live), int(alias_tables.n_alias),
+                C.c_void_p(alias_tables.rowinfo.ctypes.data), C.c_void_p(alias_tables.alias.ctypes.data),
+                len(start_nodes), C.c_void_p(start_nodes.ctypes.data), C.c_void_p(start_prefix.ctypes.data),
+                int(walker_lo), int(walker_hi))
+        tail = (int(nt), C.byref(cv), C.c_void_p(score_out.ctypes.data),
+                C.c_void_p(counters_out.ctypes.data) if counters_out is not None else None, stream)
+
+        def solve(seed):
+            check(fn(*head, int(seed) & 0xFFFFFFFFFFFFFFFF, *tail))
+        solve.keepalive = keep
+        return solve
 
 
 _engines: dict = {}

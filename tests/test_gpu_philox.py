@@ -476,3 +476,48 @@ def test_microbench_rates_are_sane(engine):
     from nrw.engine import NrwError
     with pytest.raises(NrwError):
         engine.microbench("smem_load", 10 ** 6)                  # 8 MB does not fit shared memory
+
+
+def test_host_buffer_entry_matches_device_walk(engine, c1_csr):
+    """nrw_fluence_scores_host (host buffers in, host buffers out: the call a C / ctypes user makes):
+    pinned and pageable buffers, repeated solves over the same buffers: all equal the device-resident
+    walk for every seed, id window and weight vector."""
+    import torch
+    from nrw import mesh
+    _, nc, _ = _classes(c1_csr, mesh.source_default)
+    tabs = engine.upload(c1_csr, node_class=nc)
+    at = tabs.alias_host
+    starts = np.array([435, 0, 900, 14, 899, 450], dtype=np.int32)
+    counts = np.array([3000, 0, 17, 333, 64, 2500])
+    prefix = np.concatenate([[0], np.cumsum(counts)]).astype(np.int64)
+    total = int(prefix[-1])
+
+    def pinned(a):
+        return torch.from_numpy(np.ascontiguousarray(a)).pin_memory().numpy()
+
+    class Pinned:
+        layout, n_alias = "compact", at.n_alias
+        rowinfo, alias = pinned(at.rowinfo), pinned(at.alias)
+
+    def check(view, h_starts, h_prefix, score, cnt, lo, hi, nt, cv, seeds):
+        solve = engine.prepare_fluence_scores_host(view, c1_csr.n_rows, c1_csr.n_live, h_starts, h_prefix, lo, hi,
+                                                   nt, cv, score, cnt)
+        for seed in seeds:
+            score[:] = -1
+            solve(seed)
+            ref = engine.walk(tabs, starts, counts, nt, seed, score=True, class_value=cv, walker_range=(lo, hi))
+            assert np.array_equal(score, ref.score.cpu().numpy()), (seed, lo, hi, nt, cv)
+            c = ref.counters.cpu().numpy()
+            assert [int(v) for v in cnt[:5]] == [int(v) for v in c[:5]]
+
+    p_starts, p_prefix = pinned(starts), pinned(prefix)
+    p_score, p_cnt = pinned(np.zeros(len(starts), np.int64)), pinned(np.zeros(8, np.uint64))
+    check(Pinned, p_starts, p_prefix, p_score, p_cnt, 0, total, 64, [0, 1, 0, 0], (1, 2, 3))
+    check(Pinned, p_starts, p_prefix, p_score, p_cnt, 100, total - 7, 64, [0, 1, 0, 0], (4,))          # id window
+    check(Pinned, p_starts, p_prefix, p_score, p_cnt, 0, total, 5, [0, 9, 0, 0], (5, 6))               # other kernel
+    check(Pinned, p_starts, p_prefix, p_score, p_cnt, 50, 50, 64, [0, 1, 0, 0], (7,))                  # empty window
+    # pageable buffers and fresh result buffers
+    check(at, starts.copy(), prefix.copy(), np.zeros(len(starts), np.int64), np.zeros(8, np.uint64), 0, total, 64,
+          [0, 1, 0, 0], (8, 9))
+    other_score = pinned(np.zeros(len(starts), np.int64))
+    check(Pinned, p_starts, p_prefix, other_score, p_cnt, 0, total, 64, [0, 1, 0, 0], (10,))
