@@ -267,6 +267,15 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
             tl |= TL_CNT_S; p.sm_cnt = smem; smem += align16((int)bins * 4); p.cnt_bins = (int)bins;
         } else {
             tl |= TL_CNT_G;
+            // spare shared memory becomes a cache of hot bins (walk_philox.cuh); a slot's 32-bit count
+            // cannot wrap while the launch has fewer than 2^32 walker-steps per bin: bound by walkers
+            const char* c_env = getenv("NRW_CNT_CACHE");             // NRW_CNT_CACHE=0 turns it off
+            const long long n_walkers = w->walker_hi - w->walker_lo;
+            if (!(c_env && strcmp(c_env, "0") == 0) && n_walkers < (1ll << 32)) {
+                int bits = 14;                                        // 16384 slots x 8 B = 128 KB at most
+                while (bits >= 10 && smem + (8 << bits) > e->max_smem) --bits;
+                if (bits >= 10) { p.sm_ccache = smem; p.ccache_bits = bits; smem += 8 << bits; }
+            }
         }
     }
     plan->tab = tab; plan->tl = tl; plan->smem = smem;

@@ -47,6 +47,9 @@ struct WalkParams {
     unsigned long long* work_next; long long range;
     // shared-memory carve-up (byte offsets into dynamic smem)
     int sm_rowinfo, sm_alias, sm_hist, sm_cnt;
+    // CTA-level cache of hot (t, node) bins in front of the global time-resolved counts: 2^ccache_bits
+    // (tag, count) slots at sm_ccache; 0 bits = off
+    int sm_ccache, ccache_bits;
 };
 
 template <int TAB>
@@ -134,6 +137,10 @@ walk_philox_kernel(const __grid_constant__ WalkParams p) {
         for (int i = tid; i < p.n_rows; i += WALK_THREADS) hist_s[i] = 0u;
     if constexpr (TL & TL_CNT_S)
         for (int i = tid; i < p.cnt_bins; i += WALK_THREADS) cnt_s[i] = 0u;
+    uint2* ccache_s = reinterpret_cast<uint2*>(smem + p.sm_ccache);     // .x = bin + 1 (0 = free), .y = count
+    if constexpr (TL & TL_CNT_G)
+        if (p.ccache_bits)
+            for (int i = tid; i < (1 << p.ccache_bits); i += WALK_THREADS) ccache_s[i] = make_uint2(0u, 0u);
     if constexpr (kStage) mbar_wait(bar, 0);
     __syncthreads();
 
@@ -306,11 +313,36 @@ walk_philox_kernel(const __grid_constant__ WalkParams p) {
                 }
             }
             if constexpr (TL & TL_CNT_G) {
+                const long long gq = p.per_start ? s : 0;
+                long long bin = -1;
                 if (stepped) {
-                    const long long gq = p.per_start ? s : 0;
-                    if (t < p.t_cap)
-                        atomicAdd(p.count_tn + ((size_t)(gq * p.t_cap + t) * (size_t)p.n_rows + (size_t)knew), 1u);
-                    else ++novf;
+                    if (t < p.t_cap) bin = (gq * p.t_cap + t) * (long long)p.n_rows + knew; else ++novf;
+                }
+                if (p.ccache_bits) {
+                    // Walkers of one start node move almost in lock step, so a few (t, node) bins take
+                    // most of the tallies and global atomics on them serialise in L2.  Lanes of a warp on
+                    // the same bin are merged by a vote; the merged count goes to a per-CTA shared-memory
+                    // cache of (bin, count) slots, direct-mapped by a hash; a slot belongs to the first bin
+                    // that claims it, bins that find theirs taken go to global memory directly.  The
+                    // cache is added to the global counts once, in the epilogue.
+                    const unsigned m = __match_any_sync(NRW_FULL_MASK, bin);
+                    if (bin >= 0 && lane == __ffs(m) - 1) {
+                        const uint32_t c = (uint32_t)__popc(m);
+                        bool cached = false;
+                        if (bin < 0xfffffffell) {
+                            const uint32_t tag = (uint32_t)bin + 1u;
+                            uint2* slot = ccache_s + ((tag * 2654435761u) >> (32 - p.ccache_bits));
+                            uint32_t cur_tag = *reinterpret_cast<volatile uint32_t*>(&slot->x);
+                            if (cur_tag == 0u) {
+                                cur_tag = atomicCAS(&slot->x, 0u, tag);
+                                if (cur_tag == 0u) cur_tag = tag;
+                            }
+                            if (cur_tag == tag) { atomicAdd(&slot->y, c); cached = true; }
+                        }
+                        if (!cached) atomicAdd(p.count_tn + bin, c);
+                    }
+                } else if (bin >= 0) {
+                    atomicAdd(p.count_tn + bin, 1u);
                 }
             }
 
@@ -354,6 +386,15 @@ walk_philox_kernel(const __grid_constant__ WalkParams p) {
         if (v2) atomicAdd(p.counters + 2, (unsigned long long)v2);
         if (v3) atomicAdd(p.counters + 3, (unsigned long long)v3);
         if (v4) atomicAdd(p.counters + 4, v4);
+    }
+    if constexpr (TL & TL_CNT_G) {
+        if (p.ccache_bits) {
+            __syncthreads();
+            for (int i = tid; i < (1 << p.ccache_bits); i += WALK_THREADS) {
+                const uint2 v = ccache_s[i];
+                if (v.x && v.y) atomicAdd(p.count_tn + (v.x - 1u), v.y);
+            }
+        }
     }
     if constexpr (TL & (TL_HIST_S | TL_CNT_S)) {
         __syncthreads();

@@ -78,8 +78,39 @@ def c4(M=100):
                           "walker_steps_per_s": r.walker_steps / dt, "kernel": r.kernel}), flush=True)
 
 
+def c4d(M=20_000_000, nt=40):
+    """BASELINE configs[3]: the refined mesh through the densityrw surface (time-resolved occupancy)."""
+    import torch
+    from densityrw.DensityRW import CSRTransitions, DensityRW
+    from nrw import dropin, mesh
+    csr = mesh.build_fluence_csr(0.001, 1.0 / 63.0, 200, 0.15, 1)
+    starts = [79443, 40000, 120000, 1000]
+    walk = DensityRW(nt, CSRTransitions(csr), init_walkers={(s,): M // len(starts) for s in starts})
+    np.random.seed(3)
+    walk.run(rng="philox")                                            # tables, first launch
+    t0 = time.perf_counter()
+    counts = walk.run(rng="philox")
+    t_run = time.perf_counter() - t0
+    eng, tabs = dropin.device_tables(walk.csr)
+    res = None
+    for rep in range(3):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        res = eng.walk(tabs, starts, [M // len(starts)] * len(starts), nt, 50 + rep, count_tn=True, t_cap=nt)
+        torch.cuda.synchronize()
+        t_walk = time.perf_counter() - t0
+    c = res.counters_dict()
+    print(json.dumps({"config": "C4 through densityrw.DensityRW: %d nodes, %d walkers from %d nodes, %d steps"
+                                % (csr.n_rows, M, len(starts), nt), "kernel": res.kernel,
+                      "walker_steps": c["steps"], "walk_seconds_device_resident": t_walk,
+                      "walker_steps_per_s": c["steps"] / t_walk, "DensityRW_run_seconds_host_to_host": t_run,
+                      "counts_shape": list(counts.shape), "counts_sum": float(counts.sum())}), flush=True)
+
+
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["c3", "c4"]
+    which = sys.argv[1:] or ["c3", "c4", "c4d"]
+    if "c4d" in which:
+        c4d()
     if "c3" in which:
         c3()
     if "c4" in which:
