@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define NRW_ABI_VERSION 1
+#define NRW_ABI_VERSION 2
 
 #if defined(__GNUC__)
 #define NRW_API __attribute__((visibility("default")))
@@ -52,7 +52,8 @@ typedef struct nrw_engine nrw_engine;   /* opaque handle: one per (process, devi
  *                  of fluence_mini_app.py:355-357); detcls = source class of that successor;
  *                  term = (n == 0) | detabs.  The
  *                  score kernel steps such rows without a draw (the draw cannot change the outcome).
- *         alias    (uint32 thresh, ab): target = base + ((r1 <= thresh) ? ab & 0xffff : ab >> 16)
+ *         alias    (uint32 thresh, ab): target = base + ((coin <= thresh) ? ab & 0xffff : ab >> 16),
+ *                  slot and coin = high and low word of w * n, w = one 32-bit Philox word (csrc/common.cuh)
  * WIDE    rowinfo  (uint32 off, n, base, cls)
  *         alias    (uint32 thresh, a, b, 0): target = base + ((r1 <= thresh) ? a : b)
  * A row with n == 0 is absorbing: a walker is tallied on arrival and never stepped
@@ -73,10 +74,24 @@ typedef struct nrw_tables {
     int32_t  n_alias;         /* entries in `alias`                                       */
     const void* rowinfo;      /* [n_rows] per alias_layout                                */
     const void* alias;        /* [n_alias] per alias_layout                               */
+    /* Optional, COMPACT layout only: the row descriptors in factored form, for meshes with the
+     * (direction, cell) structure of the fluence matrix (fluence_mini_app.py:331-381: live row
+     * k = i + j * fac_period; nrw/tables.py::factorise_rows builds and verifies it).  When
+     * `rowinfo` does not fit shared memory next to the alias patterns but these do, the walk derives
+     * each descriptor from them instead of loading it from global memory:
+     *   jn = j + shift[i];  inside [0, fac_cells): (dir_w0[i] | class << 30, jn * fac_period)
+     *                       outside:               (fac_exit_w0 | class << 30, fac_exit_base)
+     * All NULL / 0 when absent.                                                            */
+    const void* fac_dir;      /* uint32 [fac_period][2]: (dir_w0, shift as int32)          */
+    const void* fac_tail;     /* uint32 [fac_n_tail][2]: descriptors of rows >= n_live     */
+    const void* fac_cls;      /* uint32 [(n_live + 15) / 16]: 2-bit classes of live rows   */
+    int32_t  fac_period, fac_cells, fac_n_tail;
+    int32_t  fac_shift;       /* k / fac_period == (k * fac_magic) >> fac_shift, k < n_live */
+    uint32_t fac_magic, fac_exit_w0, fac_exit_base;
 } nrw_tables;
 
 /* ---- Philox walk (K1) -------------------------------------------------------------- */
-#define NRW_SAMPLER_ALIAS 0   /* O(1) alias draw: slot = mulhi(r0, n), coin = r1          */
+#define NRW_SAMPLER_ALIAS 0   /* O(1) alias draw (WIDE: slot = mulhi(r0, n), coin = r1)   */
 #define NRW_SAMPLER_CDF   1   /* the reference's searchsorted(left) on the fp64 prefix
                                  sums with u = ((r0>>5)*2^26 + (r1>>6)) / 2^53            */
 

@@ -165,6 +165,8 @@ struct WalkPlan {
     X(TAB_SMEM, 9) X(TAB_SMEM, 11) X(TAB_SMEM, 16) X(TAB_SMEM, 32)                             \
     X(TAB_HYB, 1) X(TAB_HYB, 3) X(TAB_HYB, 4) X(TAB_HYB, 5) X(TAB_HYB, 8) X(TAB_HYB, 9)        \
     X(TAB_HYB, 32)                                                                             \
+    X(TAB_FAC, 1) X(TAB_FAC, 3) X(TAB_FAC, 4) X(TAB_FAC, 5) X(TAB_FAC, 8) X(TAB_FAC, 9)        \
+    X(TAB_FAC, 32)                                                                             \
     X(TAB_GLB, 1) X(TAB_GLB, 3) X(TAB_GLB, 8) X(TAB_GLB, 9) X(TAB_GLB, 16) X(TAB_GLB, 32)      \
     X(TAB_CDF, 1) X(TAB_CDF, 3) X(TAB_CDF, 8) X(TAB_CDF, 9) X(TAB_CDF, 16) X(TAB_CDF, 32)
 
@@ -235,12 +237,35 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
             if (t->n_alias > (1 << 15))
                 return fail(NRW_EINVAL, "nrw_walk_philox: compact layout holds <= 2^15 alias entries");
             const int ab = align16(t->n_alias * 8), rb = align16(t->n_rows * 8);
-            if (16 + ab + rb <= e->max_smem) tab = TAB_SMEM;
+            // factored row descriptors (fluence-structured meshes): taken when the descriptor table
+            // does not fit shared memory but the three small tables do; NRW_TAB=hyb / fac overrides
+            const bool have_fac = t->fac_dir && t->fac_tail && t->fac_cls && t->fac_period > 1 &&
+                                  t->fac_cells > 0 && t->fac_n_tail == t->n_rows - t->n_live &&
+                                  (long long)t->fac_period * t->fac_cells == t->n_live;
+            const int fb = have_fac ? align16(t->fac_period * 8) + align16(t->fac_n_tail * 8) +
+                                      align16(((t->n_live + 15) / 16) * 4) : 0;
+            const char* tab_env = getenv("NRW_TAB");
+            const bool force_fac = tab_env && strcmp(tab_env, "fac") == 0, no_fac = tab_env && strcmp(tab_env, "hyb") == 0;
+            if (force_fac && !(have_fac && 16 + ab + fb <= e->max_smem))
+                return fail(NRW_EINVAL, "nrw_walk_philox: NRW_TAB=fac but the tables carry no factored rows that fit");
+            if (force_fac) tab = TAB_FAC;
+            else if (16 + ab + rb <= e->max_smem && !no_fac) tab = TAB_SMEM;
+            else if (have_fac && !no_fac && 16 + ab + fb <= e->max_smem) tab = TAB_FAC;
             else if (16 + ab <= e->max_smem) tab = TAB_HYB;
             else return fail(NRW_ENOSPC, "nrw_walk_philox: %d compact alias entries exceed shared "
                              "memory (%d B); use the wide layout", t->n_alias, e->max_smem);
             p.sm_alias = smem; smem += ab;
             if (tab == TAB_SMEM) { p.sm_rowinfo = smem; smem += rb; }
+            if (tab == TAB_FAC) {
+                p.fac_dir = t->fac_dir; p.fac_tail = t->fac_tail; p.fac_cls = t->fac_cls;
+                p.fac_period = t->fac_period; p.fac_cells = t->fac_cells; p.fac_n_tail = t->fac_n_tail;
+                p.fac_shift = t->fac_shift; p.fac_magic = t->fac_magic;
+                p.fac_exit_w0 = t->fac_exit_w0; p.fac_exit_base = t->fac_exit_base;
+                if (t->fac_shift < 0 || t->fac_shift > 31) return fail(NRW_EINVAL, "nrw_walk_philox: fac_shift=%d", t->fac_shift);
+                p.sm_fdir = smem; smem += align16(t->fac_period * 8);
+                p.sm_ftail = smem; smem += align16(t->fac_n_tail * 8);
+                p.sm_fcls = smem; smem += align16(((t->n_live + 15) / 16) * 4);
+            }
         } else {
             return fail(NRW_EINVAL, "nrw_walk_philox: alias_layout=%d", t->alias_layout);
         }
@@ -253,7 +278,7 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
     if (w->score) tl |= TL_SCORE | (w->time_weight ? TL_TW : 0);
     if (w->node_hist) {
         const int hb = align16(t->n_rows * 4);
-        if ((tab == TAB_SMEM || tab == TAB_HYB) && smem + hb <= e->max_smem) {
+        if (tab_compact(tab) && smem + hb <= e->max_smem) {
             tl |= TL_HIST_S; p.sm_hist = smem; smem += hb;
         } else {
             tl |= TL_HIST_G;
@@ -263,7 +288,7 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
         const long long groups = w->count_per_start ? w->n_starts : 1;
         const long long bins = groups * (long long)w->t_cap * t->n_rows;
         if (bins <= 0 || bins >= (1ll << 40)) return fail(NRW_EINVAL, "nrw_walk_philox: %lld count bins", bins);
-        if (tab != TAB_HYB && bins * 4 + smem <= e->max_smem && bins <= 32768) {
+        if (tab != TAB_HYB && tab != TAB_FAC && bins * 4 + smem <= e->max_smem && bins <= 32768) {
             tl |= TL_CNT_S; p.sm_cnt = smem; smem += align16((int)bins * 4); p.cnt_bins = (int)bins;
         } else {
             tl |= TL_CNT_G;
@@ -301,7 +326,7 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
 #undef X
     // score-only walks on compact tables take the trimmed kernel (walk_score.cuh); the environment
     // variable NRW_K1=general forces the general kernel (A/B measurements, parity tests of both)
-    if (tl == TL_SCORE && !w->score_sq && w->nt >= 2 && (tab == TAB_SMEM || tab == TAB_HYB)) {
+    if (tl == TL_SCORE && !w->score_sq && w->nt >= 2 && tab_compact(tab)) {
         const char* force = getenv("NRW_K1");
         const bool general = force && strcmp(force, "general") == 0;
         const bool idw = p.cwpack == 0x03020100u;
@@ -328,6 +353,7 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
 #define Y2(TAB, IDW, DET) Y(TAB, IDW, DET, 1) Y(TAB, IDW, DET, 2)
             Y2(TAB_SMEM, true, true) Y2(TAB_SMEM, false, true) Y2(TAB_HYB, true, true) Y2(TAB_HYB, false, true)
             Y2(TAB_SMEM, true, false) Y2(TAB_SMEM, false, false) Y2(TAB_HYB, true, false) Y2(TAB_HYB, false, false)
+            Y2(TAB_FAC, true, true) Y2(TAB_FAC, false, true) Y2(TAB_FAC, true, false) Y2(TAB_FAC, false, false)
 #undef Y2
             if (cps == 2) {
                 plan->block = 768;

@@ -25,7 +25,11 @@
 
 namespace nrw {
 
-enum : int { TAB_SMEM = 0, TAB_HYB = 1, TAB_GLB = 2, TAB_CDF = 3 };
+enum : int { TAB_SMEM = 0, TAB_HYB = 1, TAB_GLB = 2, TAB_CDF = 3, TAB_FAC = 4 };
+// compact alias tables (patterns in shared memory, paired draws); they differ in where a row's descriptor
+// comes from: shared memory (SMEM), global memory / L2 (HYB), or derived from three small shared-memory
+// tables on meshes with the (direction, cell) structure of the fluence matrix (FAC, fac_row below)
+__host__ __device__ constexpr bool tab_compact(int tab) { return tab == TAB_SMEM || tab == TAB_HYB || tab == TAB_FAC; }
 enum : int { TL_SCORE = 1, TL_TW = 2, TL_HIST_S = 4, TL_HIST_G = 8, TL_CNT_S = 16, TL_CNT_G = 32 };
 
 constexpr int WALK_THREADS = 1024;
@@ -50,7 +54,30 @@ struct WalkParams {
     // CTA-level cache of hot (t, node) bins in front of the global time-resolved counts: 2^ccache_bits
     // (tag, count) slots at sm_ccache; 0 bits = off
     int sm_ccache, ccache_bits;
+    // TAB_FAC (tables.py::FactoredRows): live row k = i + j * fac_period; sources of the staged tables
+    const void* fac_dir; const void* fac_tail; const void* fac_cls;
+    int fac_period, fac_cells, fac_n_tail, fac_shift;
+    uint32_t fac_magic, fac_exit_w0, fac_exit_base;
+    int sm_fdir, sm_ftail, sm_fcls;
 };
+
+// Row descriptor (w0, base) of row k derived instead of loaded (TAB_FAC): the direction table gives
+// the pattern and the cell shift, the 2-bit class table the source class; a row whose target cell lies
+// outside the mesh is an exit row.  Bit-identical to the rowinfo table it replaces (checked on the
+// host for every row before the mode is offered: tables.py::factorise_rows).
+__device__ __forceinline__ uint2 fac_row(const WalkParams& p, int k) {
+    extern __shared__ __align__(16) unsigned char smem_fac[];
+    if (k >= p.n_live) return reinterpret_cast<const uint2*>(smem_fac + p.sm_ftail)[k - p.n_live];
+    const unsigned long long prod = (unsigned long long)(uint32_t)k * p.fac_magic;
+    const uint32_t j = __funnelshift_r((uint32_t)prod, (uint32_t)(prod >> 32), p.fac_shift);   // k / period
+    const uint32_t i = (uint32_t)k - j * (uint32_t)p.fac_period;
+    const uint2 d = reinterpret_cast<const uint2*>(smem_fac + p.sm_fdir)[i];
+    const uint32_t jn = j + d.y;                                   // target cell (wraps when negative)
+    const uint32_t cls = (reinterpret_cast<const uint32_t*>(smem_fac + p.sm_fcls)[k >> 4] >> ((k & 15) * 2)) & 3u;
+    const bool leaves = jn >= (uint32_t)p.fac_cells;
+    return make_uint2((leaves ? p.fac_exit_w0 : d.x) | (cls << 30),
+                      leaves ? p.fac_exit_base : jn * (uint32_t)p.fac_period);
+}
 
 template <int TAB>
 struct RowRegs { uint32_t a, b, c, d; };   // COMPACT: a=w0 b=w1 | WIDE: off,n,base,cls | CDF: a=k b=n d=cls
@@ -63,6 +90,9 @@ __device__ __forceinline__ RowRegs<TAB> load_row(const WalkParams& p, const uint
         r.a = v.x; r.b = v.y; r.c = 0; r.d = 0;
     } else if constexpr (TAB == TAB_HYB) {
         const uint2 v = __ldg(reinterpret_cast<const uint2*>(p.rowinfo) + k);
+        r.a = v.x; r.b = v.y; r.c = 0; r.d = 0;
+    } else if constexpr (TAB == TAB_FAC) {
+        const uint2 v = fac_row(p, k);
         r.a = v.x; r.b = v.y; r.c = 0; r.d = 0;
     } else if constexpr (TAB == TAB_GLB) {
         const uint4 v = __ldg(reinterpret_cast<const uint4*>(p.rowinfo) + k);
@@ -77,12 +107,12 @@ __device__ __forceinline__ RowRegs<TAB> load_row(const WalkParams& p, const uint
 }
 template <int TAB>
 __device__ __forceinline__ uint32_t row_n(const RowRegs<TAB>& r) {
-    if constexpr (TAB == TAB_SMEM || TAB == TAB_HYB) return row_len(r.a);
+    if constexpr (tab_compact(TAB)) return row_len(r.a);
     else return r.b;
 }
 template <int TAB>
 __device__ __forceinline__ uint32_t row_cls(const RowRegs<TAB>& r) {
-    if constexpr (TAB == TAB_SMEM || TAB == TAB_HYB) return row_class(r.a);
+    if constexpr (tab_compact(TAB)) return row_class(r.a);
     else return r.d & 3u;
 }
 
@@ -93,7 +123,7 @@ __device__ __forceinline__ uint32_t row_cls(const RowRegs<TAB>& r) {
 template <int TAB>
 __device__ __forceinline__ void stage_tables_issue(const WalkParams& p, uint64_t* bar, uint2* rowinfo_s,
                                                    uint2* alias_s, int tid) {
-    if constexpr (TAB == TAB_SMEM || TAB == TAB_HYB) {
+    if constexpr (tab_compact(TAB)) {
         if (tid == 0) mbar_init(bar, 1);
         __syncthreads();
         const uint32_t alias_bytes = ((uint32_t)p.n_alias * 8u) & ~15u;
@@ -116,6 +146,16 @@ __device__ __forceinline__ void stage_tables_issue(const WalkParams& p, uint64_t
             if (TAB == TAB_SMEM && (p.n_rows & 1))
                 rowinfo_s[p.n_rows - 1] = __ldg(reinterpret_cast<const uint2*>(p.rowinfo) + p.n_rows - 1);
         }
+        if constexpr (TAB == TAB_FAC) {          // three small tables (C4: 1 KB + 8 B + 40 KB): plain loads
+            extern __shared__ __align__(16) unsigned char smem_stage[];
+            const int nthr = (int)blockDim.x;
+            uint32_t* d = reinterpret_cast<uint32_t*>(smem_stage + p.sm_fdir);
+            for (int i = tid; i < 2 * p.fac_period; i += nthr) d[i] = __ldg(reinterpret_cast<const uint32_t*>(p.fac_dir) + i);
+            d = reinterpret_cast<uint32_t*>(smem_stage + p.sm_ftail);
+            for (int i = tid; i < 2 * p.fac_n_tail; i += nthr) d[i] = __ldg(reinterpret_cast<const uint32_t*>(p.fac_tail) + i);
+            d = reinterpret_cast<uint32_t*>(smem_stage + p.sm_fcls);
+            for (int i = tid; i < (p.n_live + 15) / 16; i += nthr) d[i] = __ldg(reinterpret_cast<const uint32_t*>(p.fac_cls) + i);
+        }
     }
 }
 
@@ -131,7 +171,7 @@ walk_philox_kernel(const __grid_constant__ WalkParams p) {
     const int tid = threadIdx.x, lane = tid & 31;
 
     // ---- stage the tables: TMA bulk copies complete on one mbarrier ---------------------------
-    constexpr bool kStage = (TAB == TAB_SMEM || TAB == TAB_HYB);
+    constexpr bool kStage = tab_compact(TAB);
     stage_tables_issue<TAB>(p, bar, rowinfo_s, alias_s, tid);
     if constexpr (TL & TL_HIST_S)
         for (int i = tid; i < p.n_rows; i += WALK_THREADS) hist_s[i] = 0u;
@@ -249,7 +289,7 @@ walk_philox_kernel(const __grid_constant__ WalkParams p) {
         // ---- model steps for every live lane ------------------------------------------------------
         // compact tables: one Philox call serves a PAIR of steps (common.cuh, "paired draws"); lanes are
         // only refilled above, so every live lane is at an even t here and the warp shares the call
-        constexpr bool PAIRED = (TAB == TAB_SMEM || TAB == TAB_HYB);
+        constexpr bool PAIRED = tab_compact(TAB);
         uint2 rp = make_uint2(0u, 0u);
         if constexpr (PAIRED) {
             if (t >= 0) rp = philox2x32_10(c0, chi | (uint32_t)(t + 1), key);

@@ -33,6 +33,7 @@ namespace nrw {
 template <int TAB>
 __device__ __forceinline__ uint2 load_row2(const WalkParams& p, const uint2* rowinfo_s, int k) {
     if constexpr (TAB == TAB_SMEM) return rowinfo_s[k];
+    else if constexpr (TAB == TAB_FAC) return fac_row(p, k);
     else return __ldg(reinterpret_cast<const uint2*>(p.rowinfo) + k);
 }
 
@@ -54,7 +55,7 @@ __device__ __forceinline__ uint2 philox2x32_10_rk(uint32_t c0, uint32_t c1, cons
 template <int TAB, bool IDW, bool DET, int CPS>
 __global__ void __launch_bounds__(CPS == 1 ? 1024 : 768, CPS)
 walk_score_kernel(const __grid_constant__ WalkParams p) {
-    static_assert(TAB == TAB_SMEM || TAB == TAB_HYB, "compact alias tables only");
+    static_assert(tab_compact(TAB), "compact alias tables only");
     extern __shared__ __align__(16) unsigned char smem[];
     uint64_t* bar = reinterpret_cast<uint64_t*>(smem);
     const uint2* rowinfo_s = reinterpret_cast<const uint2*>(smem + p.sm_rowinfo);

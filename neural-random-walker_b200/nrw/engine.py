@@ -34,7 +34,11 @@ class _Tables(C.Structure):
                 ("indptr", C.c_void_p), ("cols", C.c_void_p), ("cum", C.c_void_p),
                 ("node_class", C.c_void_p),
                 ("alias_layout", C.c_int32), ("n_alias", C.c_int32),
-                ("rowinfo", C.c_void_p), ("alias", C.c_void_p)]
+                ("rowinfo", C.c_void_p), ("alias", C.c_void_p),
+                ("fac_dir", C.c_void_p), ("fac_tail", C.c_void_p), ("fac_cls", C.c_void_p),
+                ("fac_period", C.c_int32), ("fac_cells", C.c_int32), ("fac_n_tail", C.c_int32),
+                ("fac_shift", C.c_int32), ("fac_magic", C.c_uint32), ("fac_exit_w0", C.c_uint32),
+                ("fac_exit_base", C.c_uint32)]
 
 
 class _Walk(C.Structure):
@@ -131,6 +135,7 @@ class DeviceTables:
     alias: object
     struct: _Tables
     max_class: int = 0          # largest source class any row carries (weights of unused classes are free)
+    factored: tuple = ()        # device tensors of the factored row descriptors (tables.FactoredRows), if any
 
     @property
     def n_rows(self):
@@ -256,6 +261,7 @@ class Engine:
         st.indptr, st.cols, st.cum = _ptr(indptr), _ptr(cols), _ptr(cum)
         st.node_class = _ptr(nc)
         at = rowinfo = alias_t = None
+        keep_fac = ()
         st.alias_layout, st.n_alias = ALIAS_LAYOUT["none"], 0
         if alias:
             at = _tables.build_alias(csr, node_class=node_class, layout=alias_layout)
@@ -267,8 +273,18 @@ class Engine:
             alias_t = self._dev(at.alias, np.uint32)
             st.alias_layout, st.n_alias = ALIAS_LAYOUT[at.layout], at.n_alias
             st.rowinfo, st.alias = _ptr(rowinfo), _ptr(alias_t)
+            # meshes with the (direction, cell) structure of the fluence matrix: factored row descriptors,
+            # used by the walk when the descriptor table itself does not fit shared memory
+            fr = _tables.factorise_rows(at, csr.n_live) if at.layout == "compact" else None
+            if fr is not None:
+                fac = (self._dev(fr.dirtab, np.uint32), self._dev(fr.tail, np.uint32), self._dev(fr.cls_bits, np.uint32))
+                st.fac_dir, st.fac_tail, st.fac_cls = (_ptr(x) for x in fac)
+                st.fac_period, st.fac_cells, st.fac_n_tail = fr.period, fr.cells, fr.tail.shape[0]
+                st.fac_shift, st.fac_magic = fr.shift, fr.magic
+                st.fac_exit_w0, st.fac_exit_base = fr.exit_w0, fr.exit_base
+                keep_fac = fac
         max_class = 0 if node_class is None else int(np.asarray(node_class).max(initial=0))
-        return DeviceTables(csr, indptr, cols, vals, cum, nc, at, rowinfo, alias_t, st, max_class)
+        return DeviceTables(csr, indptr, cols, vals, cum, nc, at, rowinfo, alias_t, st, max_class, keep_fac)
 
     # ------------------------------------------------------------------ K1
     def _walk_struct(self, tables, start_nodes, start_counts, nt, seed, walker_range, sampler,

@@ -78,6 +78,112 @@ class AliasTables:
         return int(self.alias.shape[0])
 
 
+@dataclass
+class FactoredRows:
+    """Row descriptors of a translation-invariant mesh, factored so that they need no per-row table
+    (walk_philox.cuh::fac_row): live row r = i + j * period (direction i, cell j) is
+
+    * a *stay* row when 0 <= j + shift[i] < cells: w0 = dir_w0[i] | class << 30, base = (j + shift[i]) * period
+    * an *exit* row otherwise:                      w0 = exit_w0   | class << 30, base = exit_base
+
+    and rows >= n_live are kept verbatim in ``tail``.  ``cls_bits`` packs the 2-bit source classes of
+    the live rows 16 to a word; ``k // period == (k * magic) >> shift`` for every k < n_live."""
+    period: int
+    cells: int
+    dirtab: np.ndarray      # uint32 [period, 2]: (dir_w0[i], shift[i] as two's complement)
+    exit_w0: int
+    exit_base: int
+    tail: np.ndarray        # uint32 [n_rows - n_live, 2]
+    cls_bits: np.ndarray    # uint32 [ceil(n_live / 16)]
+    magic: int
+    shift: int
+
+    def synthesise(self, n_live: int) -> np.ndarray:
+        """The uint32 [n_live, 2] descriptors the device derives -- equal to the table they replace."""
+        k = np.arange(n_live, dtype=np.uint64)
+        j = ((k * np.uint64(self.magic)) >> np.uint64(self.shift)).astype(np.int64)
+        i = k.astype(np.int64) - j * self.period
+        jn = j + self.dirtab[i, 1].astype(np.int32).astype(np.int64)
+        out_of_mesh = (jn < 0) | (jn >= self.cells)
+        kk = k.astype(np.int64)
+        cls = (self.cls_bits[kk >> 4] >> ((kk & 15) * 2).astype(np.uint32)) & np.uint32(3)
+        w0 = np.where(out_of_mesh, np.uint32(self.exit_w0), self.dirtab[i, 0]) | (cls << np.uint32(30))
+        base = np.where(out_of_mesh, self.exit_base, jn * self.period)
+        return np.stack([w0.astype(np.uint32), base.astype(np.uint32)], axis=1)
+
+
+def factorise_rows(at: "AliasTables", n_live: int):
+    """FactoredRows of compact alias tables whose row descriptors have the (direction, cell)
+    structure of the fluence mesh (fluence_mini_app.py:331-381: row r = i + j (ND-1), a stay row
+    reaches all directions of one other cell, an exit row reaches the sink), or None.  Nothing is
+    assumed: the factored form is accepted only if it reproduces every descriptor bit for bit."""
+    if at.layout != "compact":
+        return None
+    ri = at.rowinfo
+    n_rows = ri.shape[0]
+    n_tail = n_rows - n_live
+    if n_live < 2 or not (1 <= n_tail <= 64):
+        return None
+    w0 = ri[:n_live, 0]
+    base = ri[:n_live, 1].astype(np.int64)
+    body = w0 & np.uint32(0x3FFFFFFF)
+    n = (w0 >> np.uint32(ROW_N_SHIFT)) & np.uint32(0x3FF)
+    wide = n > 1
+    if not wide.any():
+        return None
+    period = int(np.bincount(n[wide]).argmax())
+    if period < 2 or n_live % period:
+        return None
+    cells = n_live // period
+    s = int(np.ceil(np.log2(period)))
+    L = int(n_live - 1).bit_length()
+    shift = L + s
+    if shift > 31:
+        return None
+    magic = -((-(1 << shift)) // period)                    # ceil(2^shift / period)
+    if magic >= 1 << 32:
+        return None
+    r = np.arange(n_live, dtype=np.int64)
+    i, j = r % period, r // period
+    # exit rows: the most common (body, base) pair among the rows with at most one entry
+    narrow = ~wide
+    exit_w0 = exit_base = 0
+    is_exit = np.zeros(n_live, dtype=bool)
+    if narrow.any():
+        key = (body[narrow].astype(np.uint64) << np.uint64(32)) | base[narrow].astype(np.uint64)
+        vals, cnts = np.unique(key, return_counts=True)
+        top = int(vals[cnts.argmax()])
+        exit_w0, exit_base = top >> 32, top & 0xFFFFFFFF
+        is_exit = (body == np.uint32(exit_w0)) & (base == exit_base)
+    stay = ~is_exit
+    if (base[stay] % period).any():
+        return None
+    dirtab = np.zeros((period, 2), dtype=np.uint32)
+    sh_all = base // period - j
+    shifts = np.full(period, cells, dtype=np.int64)           # directions without a stay row always exit
+    first = np.full(period, -1, dtype=np.int64)
+    idx = np.nonzero(stay)[0]
+    first[i[idx][::-1]] = idx[::-1]                           # first stay row of each direction
+    have = first >= 0
+    shifts[have] = sh_all[first[have]]
+    dirtab[have, 0] = body[first[have]]
+    if np.abs(shifts).max() >= 1 << 30:
+        return None
+    dirtab[:, 1] = shifts.astype(np.int32).view(np.uint32)
+    cls = (w0 >> np.uint32(ROW_CLS_SHIFT)).astype(np.uint32)
+    words = (n_live + 15) // 16
+    padded = np.zeros(words * 16, dtype=np.uint32)
+    padded[:n_live] = cls
+    cls_bits = np.zeros(words, dtype=np.uint32)
+    for b in range(16):
+        cls_bits |= padded[b::16] << np.uint32(2 * b)
+    fr = FactoredRows(period, cells, dirtab, int(exit_w0), int(exit_base), np.ascontiguousarray(ri[n_live:]),
+                      cls_bits, int(magic), int(shift))
+    if not np.array_equal(fr.synthesise(n_live), ri[:n_live]):
+        return None
+    return fr
+
+
 def _unique_rows(key: np.ndarray):
     """(index of the first row of each distinct row, group index of every row) of a uint64 matrix.
     Rows are grouped by a 64-bit multiplicative hash (a lexicographic sort of a 158 760 x 252 key

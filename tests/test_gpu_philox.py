@@ -521,3 +521,61 @@ def test_host_buffer_entry_matches_device_walk(engine, c1_csr):
           [0, 1, 0, 0], (8, 9))
     other_score = pinned(np.zeros(len(starts), np.int64))
     check(Pinned, p_starts, p_prefix, other_score, p_cnt, 0, total, 64, [0, 1, 0, 0], (10,))
+
+
+def test_factored_row_descriptors_equal_the_table(engine, c1_csr, k1_env, monkeypatch):
+    """TAB_FAC: row descriptors derived from the (direction, cell) structure instead of loaded.  Forced
+    on the default mesh (where the table would fit shared memory) and compared with the numpy port and
+    with the table-driven kernels: score (fast and general kernel), histogram, time-resolved counts."""
+    from nrw import mesh
+    from oracle import philox_port
+    _, nc1, _ = _classes(c1_csr, mesh.source_default)
+    nc3 = (np.arange(c1_csr.n_rows) % 4).astype(np.uint8)
+    starts = np.array([435, 0, 900, 14, 14, 899, 450, 16, 464])
+    counts = np.array([3000, 0, 17, 1, 333, 64, 5, 2500, 1200])
+    for nc, cv in ((nc1, [0, 1, 0, 0]), (nc3, [5, 0, 255, 1])):
+        tabs = engine.upload(c1_csr, node_class=nc)
+        assert tabs.factored and tabs.struct.fac_period == 30 and tabs.struct.fac_cells == 30
+        for variant in ("fast", "fast_nodet", "general"):
+            k1_env(variant)
+            monkeypatch.setenv("NRW_TAB", "fac")
+            for nt in (64, 3, 2):
+                res = engine.walk(tabs, starts, counts, nt, 5, score=True, class_value=cv)
+                assert "TAB_FAC" in res.kernel, res.kernel
+                port = philox_port.walk_port(c1_csr, starts, counts, nt, 5, alias=tabs.alias_host, class_value=cv)
+                _cmp(res, port, hist=False)
+            monkeypatch.delenv("NRW_TAB")
+    k1_env("fast")
+    monkeypatch.setenv("NRW_TAB", "fac")
+    tabs = engine.upload(c1_csr, node_class=nc1)
+    res = engine.walk(tabs, starts, counts, 50, 8, score=True, node_hist=True, class_value=[0, 1, 0, 0])
+    assert "TAB_FAC" in res.kernel
+    port = philox_port.walk_port(c1_csr, starts, counts, 50, 8, alias=tabs.alias_host, class_value=[0, 1, 0, 0])
+    _cmp(res, port, hist=True)
+    res = engine.walk(tabs, [435, 14], [5000, 700], 40, 9, count_tn=True, t_cap=40, count_per_start=True)
+    assert "TAB_FAC" in res.kernel
+    port = philox_port.walk_port(c1_csr, [435, 14], [5000, 700], 40, 9, alias=tabs.alias_host, t_cap=40,
+                                 count_per_start=True)
+    _cmp(res, port, score=False, hist=False, count=True)
+
+
+def test_refined_mesh_factored_equals_l2_resident_descriptors(engine, monkeypatch):
+    """C4 (158 760 nodes): the planner takes TAB_FAC; scores and counters equal the TAB_HYB walk."""
+    from nrw import mesh, tables
+    csr = mesh.build_fluence_csr(0.001, 1.0 / 63.0, 200, 0.15, 1)
+    src = mesh.source_values(csr.meta["mesh"]["meshpoints"], mesh.source_default)
+    nc, _ = tables.classify_source(src, csr.n_rows)
+    tabs = engine.upload(csr, node_class=nc)
+    assert tabs.factored and tabs.struct.fac_period == 126 and tabs.struct.fac_cells == 1260
+    starts = np.arange(0, csr.n_live, 7)
+    out = {}
+    for mode in ("fac", "hyb"):
+        monkeypatch.setenv("NRW_TAB", mode)
+        res = engine.walk(tabs, starts, 40, 30000, 3, score=True, class_value=[0, 1, 0, 0])
+        assert ("TAB_FAC" if mode == "fac" else "TAB_HYB") in res.kernel, res.kernel
+        out[mode] = (res.score.cpu().numpy(), res.counters.cpu().numpy()[:5])
+    monkeypatch.delenv("NRW_TAB")
+    res = engine.walk(tabs, starts, 40, 30000, 3, score=True, class_value=[0, 1, 0, 0])
+    assert "TAB_FAC" in res.kernel                                   # the planner's own choice
+    assert np.array_equal(out["fac"][0], out["hyb"][0]) and np.array_equal(out["fac"][1], out["hyb"][1])
+    assert np.array_equal(res.score.cpu().numpy(), out["hyb"][0])

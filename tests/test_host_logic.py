@@ -283,3 +283,32 @@ def test_port_sharding_invariance_and_statistics(c1_csr):
     sig = np.sqrt(var[starts] / M)
     z = np.abs(est - mean[starts]) / np.where(sig > 0, sig, 1)
     assert z.max() < 4.5 and (est[sig == 0] == mean[starts][sig == 0]).all()
+
+
+def test_factorise_rows_is_exact_or_absent():
+    """tables.factorise_rows: the factored descriptors reproduce the table bit for bit on fluence
+    meshes (any source classes), and graphs without that structure are refused."""
+    from nrw import mesh, tables
+    for dt, da in ((0.01, 1.0 / 15.0), (0.005, 1.0 / 15.0), (0.01, 0.2), (0.005, 0.04)):
+        csr = mesh.build_fluence_csr(dt, da, 200, 0.15, 1)
+        for nc in (None, (np.arange(csr.n_rows) * 7 % 4).astype(np.uint8)):
+            at = tables.build_alias(csr, node_class=nc)
+            fr = tables.factorise_rows(at, csr.n_live)
+            assert fr is not None and fr.period * fr.cells == csr.n_live
+            assert np.array_equal(fr.synthesise(csr.n_live), at.rowinfo[:csr.n_live])
+            assert np.array_equal(fr.tail, at.rowinfo[csr.n_live:])
+            k = np.arange(csr.n_live, dtype=np.uint64)
+            assert np.array_equal((k * np.uint64(fr.magic)) >> np.uint64(fr.shift), k // np.uint64(fr.period))
+    q = mesh.build_simple_flux_dense(0.005, 8.0, 2.0)
+    c = mesh.csr_from_dense(q, n_live=2)
+    assert tables.factorise_rows(tables.build_alias(c), c.n_live) is None
+    rng = np.random.default_rng(0)
+    q = rng.random((40, 40)) * (rng.random((40, 40)) < 0.2)
+    q[:, 0] += 1e-3
+    c = mesh.csr_from_dense(q / q.sum(axis=1, keepdims=True), n_live=39)
+    assert tables.factorise_rows(tables.build_alias(c), c.n_live) is None
+    # one perturbed descriptor breaks the structure: refused, never approximated
+    csr = mesh.build_fluence_csr(0.01, 1.0 / 15.0, 200, 0.15, 1)
+    at = tables.build_alias(csr)
+    at.rowinfo[100, 1] += 30
+    assert tables.factorise_rows(at, csr.n_live) is None
