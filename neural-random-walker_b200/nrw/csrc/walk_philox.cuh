@@ -373,9 +373,9 @@ walk_philox_kernel(const __grid_constant__ WalkParams p) {
                             const uint32_t tag = (uint32_t)bin + 1u;
                             uint2* slot = ccache_s + ((tag * 2654435761u) >> (32 - p.ccache_bits));
                             uint32_t cur_tag = *reinterpret_cast<volatile uint32_t*>(&slot->x);
-                            if (cur_tag == 0u) {
-                                cur_tag = atomicCAS(&slot->x, 0u, tag);
-                                if (cur_tag == 0u) cur_tag = tag;
+                            if (cur_tag == 0u && c >= 2u) {       // only bins that are hot NOW claim a slot:
+                                cur_tag = atomicCAS(&slot->x, 0u, tag);   // keeps the long tail of rarely
+                                if (cur_tag == 0u) cur_tag = tag;         // visited bins out of the cache
                             }
                             if (cur_tag == tag) { atomicAdd(&slot->y, c); cached = true; }
                         }
