@@ -115,18 +115,24 @@ def test_wide_global_tables_bit_exact(engine, c1_csr):
     _cmp(res, port)
 
 
-def test_hybrid_tables_bit_exact(engine):
-    """38 441-row mesh: alias patterns fit shared memory, row descriptors (300 KB) stay in L2."""
+def test_hybrid_tables_bit_exact(engine, monkeypatch):
+    """38 441-row mesh: alias patterns fit shared memory, the row descriptors (300 KB) do not: they stay
+    in L2 (TAB_HYB, forced here) or are derived from the factored tables (TAB_FAC, the planner's choice)."""
     from nrw import mesh
     from oracle import philox_port
     csr = mesh.build_fluence_csr(0.001, 1.0 / 31.0, 200, 0.15, 1)
     _, nc, _ = _classes(csr, mesh.source_default)
     tabs = engine.upload(csr, node_class=nc)
     starts = np.arange(0, csr.n_live, 97)
-    res = engine.walk(tabs, starts, 16, 400, 6, score=True, class_value=[0, 1, 0, 0], node_hist=True)
-    assert "TAB_HYB" in res.kernel
     port = philox_port.walk_port(csr, starts, 16, 400, 6, alias=tabs.alias_host, class_value=[0, 1, 0, 0])
-    _cmp(res, port)
+    for mode, want in (("hyb", "TAB_HYB"), (None, "TAB_FAC")):
+        if mode:
+            monkeypatch.setenv("NRW_TAB", mode)
+        else:
+            monkeypatch.delenv("NRW_TAB", raising=False)
+        res = engine.walk(tabs, starts, 16, 400, 6, score=True, class_value=[0, 1, 0, 0], node_hist=True)
+        assert want in res.kernel, res.kernel
+        _cmp(res, port)
 
 
 def test_simple_flux_counts_smem_bit_exact(engine):
@@ -351,9 +357,9 @@ def test_score_fast_path_bit_exact_all_variants(engine, c1_csr, k1_env, variant)
     _cmp(res, port, hist=False)
 
 
-def test_score_fast_path_hybrid_tables_and_survivors(engine, k1_env):
-    """Row descriptors in L2 (TAB_HYB) + walkers that outlive nt (survivors; the step t = nt-1 is
-    outside the solution sum, fluence_mini_app.py:428)."""
+def test_score_fast_path_hybrid_tables_and_survivors(engine, k1_env, monkeypatch):
+    """Row descriptors in L2 (TAB_HYB) or derived (TAB_FAC) + walkers that outlive nt (survivors; the
+    step t = nt-1 is outside the solution sum, fluence_mini_app.py:428)."""
     from nrw import mesh
     from oracle import philox_port
     k1_env("fast")
@@ -362,10 +368,15 @@ def test_score_fast_path_hybrid_tables_and_survivors(engine, k1_env):
     tabs = engine.upload(csr, node_class=nc)
     starts = np.arange(0, csr.n_live, 97)
     for nt in (400, 9):                                  # nt = 9: most walkers survive
-        res = engine.walk(tabs, starts, 48, nt, 6, score=True, class_value=[0, 1, 0, 0])
-        assert "walk_score<TAB_HYB" in res.kernel, res.kernel
         port = philox_port.walk_port(csr, starts, 48, nt, 6, alias=tabs.alias_host, class_value=[0, 1, 0, 0])
-        _cmp(res, port, hist=False)
+        for mode, want in (("hyb", "walk_score<TAB_HYB"), (None, "walk_score<TAB_FAC")):
+            if mode:
+                monkeypatch.setenv("NRW_TAB", mode)
+            else:
+                monkeypatch.delenv("NRW_TAB", raising=False)
+            res = engine.walk(tabs, starts, 48, nt, 6, score=True, class_value=[0, 1, 0, 0])
+            assert want in res.kernel, res.kernel
+            _cmp(res, port, hist=False)
     assert port["counters"]["survivors"] > 0
 
 
