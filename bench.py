@@ -465,7 +465,7 @@ def resource_leg(eng, tabs, starts, Mg, id_base, flush, steps_per_launch, kernel
     # score kernel: two dependent shared-memory look-ups per drawn step (alias entry, row descriptor)
     lds = 2.0 * steps_per_launch * (1.0 - det_frac) / (kernel_ms * 1e-3)
     out["score_kernel"] = {"smem_loads_per_s": lds, "frac_of_smem_load_peak": lds / peaks["smem_random_load_8B_per_s"]}
-    # occupancy-histogram mode: one shared-memory atomic per walker-step (sink arrivals are vote-aggregated)
+    # occupancy-histogram mode: one shared-memory atomic per walker-step (sink arrivals are counted in registers)
     hl, hres = eng.prepare_walk(tabs, starts, Mg, NT, seed=1, score=True, class_value=[0, 1, 0, 0],
                                 node_hist=True, start_id_base=id_base)
     for _ in range(3):

@@ -53,13 +53,14 @@ __host__ __device__ __forceinline__ uint32_t seed_to_key(uint64_t seed) {
 }
 
 // ---- COMPACT row descriptor word 0 (include/nrw.h): off[0:15) | n[15:25) | detcls[25:27) | detabs[27] |
-//      term[28] | spare[29] | cls[30:32).  detabs marks a row whose single successor is absorbing; detcls
-//      is that successor's source class; term = (n == 0) | detabs: a walker landing here ends in this
-//      iteration (tables.py::build_alias).
+//      term[28] | detlast[29] | cls[30:32).  detabs marks a row whose single successor is absorbing; detcls
+//      is that successor's source class; detlast: that successor is the last row (the fluence sink);
+//      term = (n == 0) | detabs: a walker landing here ends in this iteration (tables.py::build_alias).
 constexpr uint32_t ROW_OFF_MASK = 0x00007fffu;
 constexpr uint32_t ROW_N_MASK   = 0x01ff8000u;
 constexpr uint32_t ROW_DETABS   = 0x08000000u;
 constexpr uint32_t ROW_TERM     = 0x10000000u;
+constexpr uint32_t ROW_DETLAST  = 0x20000000u;
 __host__ __device__ __forceinline__ uint32_t row_off(uint32_t w0) { return w0 & ROW_OFF_MASK; }
 __host__ __device__ __forceinline__ uint32_t row_len(uint32_t w0) { return (w0 >> 15) & 0x3ffu; }
 __host__ __device__ __forceinline__ uint32_t row_detcls(uint32_t w0) { return (w0 >> 25) & 3u; }

@@ -326,7 +326,9 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
 #undef X
     // score-only walks on compact tables take the trimmed kernel (walk_score.cuh); the environment
     // variable NRW_K1=general forces the general kernel (A/B measurements, parity tests of both)
-    if (tl == TL_SCORE && !w->score_sq && w->nt >= 2 && tab_compact(tab)) {
+    if ((tl == TL_SCORE || tl == TL_HIST_S || tl == (TL_SCORE | TL_HIST_S)) && !w->score_sq && w->nt >= 2 &&
+        tab_compact(tab)) {
+        const bool hist = (tl & TL_HIST_S) != 0;
         const char* force = getenv("NRW_K1");
         const bool general = force && strcmp(force, "general") == 0;
         const bool idw = p.cwpack == 0x03020100u;
@@ -345,10 +347,15 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
             // two CTAs of 768 threads per SM when the tables leave room (NRW_CPS=1 forces one CTA)
             const char* cps_env = getenv("NRW_CPS");
             const int cps = (plan->smem <= 112 * 1024 && !(cps_env && strcmp(cps_env, "1") == 0)) ? 2 : 1;
-#define Y(TAB, IDW, DET, CPS)                                                  \
-    if (tab == TAB && idw == IDW && det == DET && cps == CPS) {                \
-        plan->fn = (const void*)walk_score_kernel<TAB, IDW, DET, CPS>;         \
-        plan->name = "walk_score<" #TAB "," #IDW "," #DET ",cps=" #CPS ">";    \
+#define Y(TAB, IDW, DET, CPS)                                                       \
+    if (tab == TAB && idw == IDW && det == DET && cps == CPS) {                     \
+        if (hist) {                                                                 \
+            plan->fn = (const void*)walk_score_kernel<TAB, IDW, DET, CPS, true>;    \
+            plan->name = "walk_score_hist<" #TAB "," #IDW "," #DET ",cps=" #CPS ">"; \
+        } else {                                                                    \
+            plan->fn = (const void*)walk_score_kernel<TAB, IDW, DET, CPS, false>;   \
+            plan->name = "walk_score<" #TAB "," #IDW "," #DET ",cps=" #CPS ">";     \
+        }                                                                           \
     }
 #define Y2(TAB, IDW, DET) Y(TAB, IDW, DET, 1) Y(TAB, IDW, DET, 2)
             Y2(TAB_SMEM, true, true) Y2(TAB_SMEM, false, true) Y2(TAB_HYB, true, true) Y2(TAB_HYB, false, true)

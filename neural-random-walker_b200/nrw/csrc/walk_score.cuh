@@ -52,7 +52,10 @@ __device__ __forceinline__ uint2 philox2x32_10_rk(uint32_t c0, uint32_t c1, cons
 
 // CPS = CTAs per SM: 1 -> 1024 threads (tables up to 227 KB), 2 -> two CTAs of 768 threads when the
 // tables fit half an SM's shared memory (48 instead of 32 resident warps).
-template <int TAB, bool IDW, bool DET, int CPS>
+// HIST: also tally every in-sum step at its target node (the occupancy histogram of walk_philox.cuh,
+// TL_HIST_S): shared-memory atomics for the nodes walkers spread over, a per-lane register count for
+// the one node they all end on (the last row: the sink), one merge into global memory per CTA.
+template <int TAB, bool IDW, bool DET, int CPS, bool HIST = false>
 __global__ void __launch_bounds__(CPS == 1 ? 1024 : 768, CPS)
 walk_score_kernel(const __grid_constant__ WalkParams p) {
     static_assert(tab_compact(TAB), "compact alias tables only");
@@ -60,11 +63,15 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
     uint64_t* bar = reinterpret_cast<uint64_t*>(smem);
     const uint2* rowinfo_s = reinterpret_cast<const uint2*>(smem + p.sm_rowinfo);
     const uint2* alias_s = reinterpret_cast<const uint2*>(smem + p.sm_alias);
+    uint32_t* hist_s = reinterpret_cast<uint32_t*>(smem + p.sm_hist);
     const int tid = threadIdx.x, lane = tid & 31;
     stage_tables_issue<TAB>(p, bar, reinterpret_cast<uint2*>(smem + p.sm_rowinfo),
                             reinterpret_cast<uint2*>(smem + p.sm_alias), tid);
+    if constexpr (HIST)
+        for (int i = tid; i < p.n_rows; i += (int)blockDim.x) hist_s[i] = 0u;
     mbar_wait(bar, 0);
     __syncthreads();
+    const int sink_row = p.n_rows - 1;           // HIST: the node every exit ends on is counted in registers
 
     const int t_last = p.t_last;                 // nt - 1: last model step (fluence_mini_app.py:236); >= 1 here
     const uint32_t lt_mask = lanemask_lt();
@@ -78,6 +85,9 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
     uint32_t s_end_off = 0, c0_base = 0, chi_base = 0;
     int t_init = 0;
     uint32_t det_w = 0, det_n = 0;               // DET: walkers of a deterministic-exit start
+    uint32_t det_hs = 0, det_hn = 0;             // HIST: their one in-sum tally lands on the sink / on det_tgt
+    int det_tgt = 0;
+    uint32_t nsink = 0;                          // HIST: in-sum arrivals on sink_row
     uint2 srow = make_uint2(0, 0);
     uint32_t x = 0;                              // score of the lane's walkers of start s since the last flush
                                                  // (flushed at a range fetch once it passes 2^31; planner bound: range * nt * weight < 2^31)
@@ -92,8 +102,15 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
     auto weight_of = [&](uint32_t cls) -> uint32_t {
         return IDW ? cls : ((p.cwpack >> (cls * 8u)) & 0xffu);
     };
+    auto tally_node = [&](int k, uint32_t c) {   // HIST (callers make sure the step is inside the sum)
+        if (k == sink_row) nsink += c;
+        else atomicAdd(hist_s + k, c);
+    };
+    auto det_target = [&](uint32_t w0, uint32_t base) -> int {   // the single successor of a detabs row
+        return (int)(base + (alias_s[row_off(w0)].y & 0xffffu));
+    };
     auto flush_score = [&]() {
-        if (s >= 0 && x != 0)
+        if (p.score && s >= 0 && x != 0)
             atomicAdd(reinterpret_cast<unsigned long long*>(p.score) + s, (unsigned long long)x);
         x = 0;
     };
@@ -152,6 +169,12 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
             det_n = det ? 1u : 0u;
             det_w = (det && t_last >= 2) ? weight_of(row_detcls(srow.x)) : 0u;   // t = nt-1 is outside the sum
             if (det) t_init = -1;
+            if constexpr (HIST) {
+                det_tgt = det ? det_target(srow.x, srow.y) : 0;
+                const bool in_sum = det && t_last >= 2;
+                det_hs = (in_sum && det_tgt == sink_row) ? 1u : 0u;
+                det_hn = (in_sum && det_tgt != sink_row) ? 1u : 0u;
+            }
         }
     };
     auto take = [&](uint32_t off) {
@@ -160,7 +183,10 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
         chi = chi_base;
         ra = srow.x; rb = srow.y;
         t = t_init;
-        if constexpr (DET) { x += det_w; nst += det_n; }
+        if constexpr (DET) {
+            x += det_w; nst += det_n;
+            if constexpr (HIST) { nsink += det_hs; if (det_hn) [[unlikely]] atomicAdd(hist_s + det_tgt, 1u); }
+        }
     };
 
     while (true) {
@@ -179,6 +205,7 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
                     const uint32_t k = (lim - cur - (uint32_t)lane + 31u) >> 5;
                     x += det_w * k;
                     nst += k;
+                    if constexpr (HIST) { nsink += det_hs * k; if (det_hn) [[unlikely]] atomicAdd(hist_s + det_tgt, k); }
                     cur = lim;
                     continue;
                 }
@@ -232,6 +259,13 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
                     // an absorbing row, or (DET) a row whose single successor is absorbing (fluence exit
                     // rows, fluence_mini_app.py:355-357): that step is taken now -- no draw could change it
                     // (detcls is 0 on every row that is not such an exit row)
+                    if constexpr (HIST) {
+                        tally_node(knew, 1u);
+                        if constexpr (DET) {
+                            if (row.x & ROW_DETLAST) ++nsink;                         // the exit step, onto the sink
+                            else if (row.x & ROW_DETABS) [[unlikely]] tally_node(det_target(row.x, row.y), 1u);
+                        }
+                    }
                     if constexpr (DET && IDW) {
                         x += row_detcls(row.x);
                         nst += (row.x >> 27) & 1u;
@@ -244,11 +278,12 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
                     int tl = tn;
                     bool absorbed = (row.x & ROW_N_MASK) == 0u;
                     uint32_t wl = weight_of(row_class(row.x));
+                    if constexpr (HIST) { if (tn < t_last) tally_node(knew, 1u); }
                     if constexpr (DET) {
                         if (!absorbed && tn < t_last) {
                             wl = weight_of(row_detcls(row.x));
                             x += wl;
-                            tl = tn + 1;
+                            tl = tn + 1;              // == t_last: outside the sum, no histogram tally
                             absorbed = true;
                         }
                     }
@@ -259,6 +294,8 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
                     nst += (uint32_t)tl;
                 }
                 t = -1;
+            } else {
+                if constexpr (HIST) atomicAdd(hist_s + knew, 1u);
             }
         };
         // one Philox call serves the two steps of a pair (common.cuh, "paired draws"): lanes are refilled
@@ -288,6 +325,16 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
         if (wwalk - v2) atomicAdd(p.counters + 1, wwalk - v2);          // exits = walkers - survivors
         if (v2) atomicAdd(p.counters + 2, (unsigned long long)v2);
         if (wwalk) atomicAdd(p.counters + 4, wwalk);
+    }
+    if constexpr (HIST) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) nsink += __shfl_xor_sync(NRW_FULL_MASK, nsink, o);
+        if (lane == 0 && nsink) atomicAdd(hist_s + sink_row, nsink);
+        __syncthreads();
+        for (int i = tid; i < p.n_rows; i += (int)blockDim.x) {
+            const uint32_t h = hist_s[i];
+            if (h) atomicAdd(p.node_hist + i, (unsigned long long)h);
+        }
     }
 }
 

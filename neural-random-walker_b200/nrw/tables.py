@@ -26,7 +26,7 @@ from .mesh import TransitionCSR
 COMPACT_MAX_N = 1023
 COMPACT_MAX_REL = 65535
 COMPACT_MAX_ENTRIES = 1 << 15          # offsets are 15 bits: what one SM's shared memory can hold anyway
-ROW_N_SHIFT, ROW_DETCLS_SHIFT, ROW_DETABS_BIT, ROW_TERM_BIT, ROW_CLS_SHIFT = 15, 25, 27, 28, 30
+ROW_N_SHIFT, ROW_DETCLS_SHIFT, ROW_DETABS_BIT, ROW_TERM_BIT, ROW_DETLAST_BIT, ROW_CLS_SHIFT = 15, 25, 27, 28, 29, 30
 
 
 def row_cum(csr: TransitionCSR) -> np.ndarray:
@@ -290,8 +290,10 @@ def build_alias(csr: TransitionCSR, node_class: np.ndarray | None = None,
         first = csr.cols[np.minimum(csr.indptr[:-1], max(csr.nnz - 1, 0))].astype(np.int64) if csr.nnz else np.zeros(n, np.int64)
         detabs = (row_n == 1) & (row_n[first] == 0)
         detcls = np.where(detabs, node_class[first], 0).astype(np.uint32)
+        detlast = detabs & (first == n - 1)                    # ... and it is the last row (the fluence sink)
         w0 = (row_off | (row_n << np.uint32(ROW_N_SHIFT)) | (detcls << np.uint32(ROW_DETCLS_SHIFT))
               | (detabs.astype(np.uint32) << np.uint32(ROW_DETABS_BIT))
+              | (detlast.astype(np.uint32) << np.uint32(ROW_DETLAST_BIT))
               | ((detabs | (row_n == 0)).astype(np.uint32) << np.uint32(ROW_TERM_BIT))
               | (node_class << np.uint32(ROW_CLS_SHIFT)))
         rowinfo = np.stack([w0, row_base], axis=1).astype(np.uint32)

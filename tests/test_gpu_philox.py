@@ -349,6 +349,11 @@ def test_score_fast_path_bit_exact_all_variants(engine, c1_csr, k1_env, variant)
             port = philox_port.walk_port(c1_csr, starts, counts, nt, 5, alias=tabs.alias_host, class_value=cv,
                                          walker_range=rng_, start_id_base=idb)
             _cmp(res, port, hist=False)
+            res = engine.walk(tabs, starts, counts, nt, 5, score=True, class_value=cv, walker_range=rng_,
+                              start_id_base=idb, node_hist=True)                  # + occupancy histogram
+            if nt >= 2:
+                assert ("walk_philox<" if variant == "general" else "walk_score_hist<TAB_SMEM") in res.kernel
+            _cmp(res, port, hist=True)
     # a long uniform start list: many range fetches and start changes per warp
     tabs = engine.upload(c1_csr, node_class=nc1)
     res = engine.walk(tabs, np.arange(900), 777, 64, 6, score=True, class_value=[0, 1, 0, 0])
@@ -476,6 +481,13 @@ def test_random_graphs_differential(engine, k1_env, seed):
         res = engine.walk(tabs, starts, counts, nt, seed, score=True, class_value=cv, walker_range=window,
                           start_id_base=idb)
         _cmp(res, port, hist=False)
+        # the same walk with the occupancy histogram (walk_score_hist / general kernel), and histogram only
+        res = engine.walk(tabs, starts, counts, nt, seed, score=True, class_value=cv, walker_range=window,
+                          start_id_base=idb, node_hist=True)
+        assert ("walk_philox<" if variant == "general" else "walk_score_hist<") in res.kernel, res.kernel
+        _cmp(res, port, hist=True)
+        res = engine.walk(tabs, starts, counts, nt, seed, node_hist=True, walker_range=window, start_id_base=idb)
+        _cmp(res, port, score=False, hist=True)
 
 
 def test_microbench_rates_are_sane(engine):
