@@ -11,9 +11,11 @@ The reference samples a transition with ``np.searchsorted(np.cumsum(myQ,axis=1)[
   the 10 001-node mesh needs 80 KB of patterns + 80 KB of row descriptors, which is what lets the
   kernel stage everything in one SM's shared memory.
 
-Quantisation: the alias coin is a 32-bit threshold (probabilities resolved to 2^-32) and the slot
-is ``mulhi(r0, n)`` (slot probabilities equal to within n/2^32) -- both orders of magnitude below
-the Monte-Carlo error of any feasible run and stated in DESIGN.md.
+Quantisation: the alias coin is compared with a 32-bit threshold.  On the compact layout slot and
+coin are the high and low word of ``w * n`` for ONE 32-bit Philox word ``w`` (csrc/common.cuh, "paired
+draws"): both deviate from uniform by less than n/2^32; on the wide layout the slot is
+``mulhi(r0, n)`` and the coin a second word (resolved to 2^-32).  All orders of magnitude below the
+Monte-Carlo error of any feasible run and stated in DESIGN.md.
 """
 from __future__ import annotations
 
