@@ -4,6 +4,7 @@
 
 #include <cstdarg>
 #include <cstdio>
+#include <algorithm>
 #include <cstring>
 
 #include "common.cuh"
@@ -330,8 +331,14 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
         tab_compact(tab)) {
         const bool hist = (tl & TL_HIST_S) != 0;
         const char* force = getenv("NRW_K1");
-        const bool general = force && strcmp(force, "general") == 0;
+        bool general = force && strcmp(force, "general") == 0;
         const bool idw = p.cwpack == 0x03020100u;
+        {   // the trimmed kernel keeps 32-bit running sums per lane (see below): walks so long that even a
+            // 32-id range could wrap them stay with the general kernel
+            long long mw = 3;
+            if (!idw) for (int i = 0; i < 4; ++i) mw = std::max(mw, (long long)((p.cwpack >> (8 * i)) & 0xffu));
+            if (32ll * (long long)w->nt * mw >= (1ll << 31)) general = true;
+        }
         const char* det_env = getenv("NRW_DET");             // NRW_DET=0: draw on deterministic rows too
         const bool det = !(det_env && strcmp(det_env, "0") == 0);
         if (!general) {

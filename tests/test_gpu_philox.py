@@ -602,3 +602,19 @@ def test_refined_mesh_factored_equals_l2_resident_descriptors(engine, monkeypatc
     assert "TAB_FAC" in res.kernel                                   # the planner's own choice
     assert np.array_equal(out["fac"][0], out["hyb"][0]) and np.array_equal(out["fac"][1], out["hyb"][1])
     assert np.array_equal(res.score.cpu().numpy(), out["hyb"][0])
+
+
+def test_very_long_time_horizons_stay_with_the_general_kernel(engine, c1_csr):
+    """The trimmed kernel keeps 32-bit running sums per lane; the planner only picks it when a 32-id
+    range cannot wrap them (32 * nt * max weight < 2^31)."""
+    from nrw import mesh
+    from oracle import philox_port
+    _, nc, _ = _classes(c1_csr, mesh.source_default)
+    tabs = engine.upload(c1_csr, node_class=nc)
+    starts, counts = [435, 14], [500, 300]
+    res = engine.walk(tabs, starts, counts, 1 << 23, 3, score=True, class_value=[0, 255, 0, 0])
+    assert "walk_philox<" in res.kernel, res.kernel
+    port = philox_port.walk_port(c1_csr, starts, counts, 1 << 23, 3, alias=tabs.alias_host, class_value=[0, 255, 0, 0])
+    _cmp(res, port, hist=False)
+    res = engine.walk(tabs, starts, counts, 1 << 18, 3, score=True, class_value=[0, 255, 0, 0])
+    assert "walk_score<" in res.kernel, res.kernel
