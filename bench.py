@@ -230,7 +230,8 @@ def workload_config(args):
                         "BASELINE configs[4]), nt=30000, default source, rng=philox, sampler=alias"
                         % args.walkers_per_node_per_gpu,
             "walkers_per_node_per_gpu": args.walkers_per_node_per_gpu, "n_nodes": 10000,
-            "tally": args.tally, "parallelism": "walker-id sharding, 1 NCCL allreduce of the score buffer",
+            "tally": args.tally, "parallelism": "walker-id sharding; one all-reduce of the score buffer per step "
+                                                "(N > 1: a single kernel over NVLink peer memory, NCCL as fall-back)",
             "l2": "tables are shared-memory resident by design; a 512 MiB buffer is overwritten "
                   "between timed steps (untimed) to flush L2"}
 
@@ -262,14 +263,25 @@ def run_ours(args):
     starts = np.arange(n_nodes)
     id_base = starts.astype(np.int64) * M_total + rank * Mg      # rank's slice of every start's walkers
     want_hist = args.tally == "score+hist"
-    launch, res = eng.prepare_walk(tabs, starts, Mg, NT, seed=1, score=True, class_value=[0, 1, 0, 0],
-                                   node_hist=want_hist, start_id_base=id_base)
+    # N > 1: the one collective of the path runs as one kernel over NVLink peer memory (nrw.dist.
+    # ScoreAllReduce, NCCL fall-back); the walk of step k writes score buffer k & 1 directly
+    red = ndist.ScoreAllReduce(n_nodes, eng) if world > 1 else None
+    pws = []
+    for h in range(2 if red is not None else 1):
+        pws.append(eng.prepare_walk(tabs, starts, Mg, NT, seed=1, class_value=[0, 1, 0, 0], node_hist=want_hist,
+                                    start_id_base=id_base, score=True if red is None else red.half(h)))
+    if red is not None:                           # reduce() zeroes the score buffer of the next step itself
+        for pw, r in pws:
+            pw.tallies = [t for t in pw.tallies if t is not r.score]
+    launch, res = pws[0]
     flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
 
     def step():
-        launch()
-        if world > 1:
-            tdist.all_reduce(res.score, op=tdist.ReduceOp.SUM)    # the single collective of the path
+        if red is None:
+            launch()
+        else:
+            pws[red.epoch & 1][0]()                                # zero + walk into this epoch's buffer
+            red.reduce()                                           # the single collective of the path
 
     def barrier():
         if world > 1:
@@ -294,6 +306,14 @@ def run_ours(args):
         barrier()
         t_wall = time.perf_counter() - t_wall
     ms = np.array([a.elapsed_time(b) for a, b in evs])
+    collective = None
+    if red is not None:
+        red.check()                                               # no rank timed out in a reduction
+        # the last reduction against NCCL on the same per-rank vector (integer sum: must be identical)
+        chk = red.half((red.epoch - 1) & 1).clone()
+        tdist.all_reduce(chk, op=tdist.ReduceOp.SUM)
+        assert torch.equal(chk, red.out), "ScoreAllReduce differs from NCCL all_reduce"
+        collective = "one kernel over NVLink peer memory (nrw_p2p_allreduce_i64)" if red.p2p else "NCCL all_reduce"
     total_ms = torch.tensor([float(ms.sum())], dtype=torch.float64, device=dev)
     steps_t = torch.tensor([steps_per_launch], dtype=torch.int64, device=dev)
     if world > 1:
@@ -387,8 +407,9 @@ def run_ours(args):
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32/f64",
                 "data": "synthetic", "config": workload_config(args), "roofline": roofline,
                 "walker_steps_per_step": job_steps, "walkers_per_step": n_nodes * Mg * world,
-                "gpu_launches": args.steps, "wall_s_timed_region": t_wall,
-                "launch_geometry": list(res.launch_geometry), "ablation_kernel_only": ablation or None}
+                "gpu_launches": args.steps * (2 if (red is not None and red.p2p) else 1), "wall_s_timed_region": t_wall,
+                "launch_geometry": list(res.launch_geometry), "ablation_kernel_only": ablation or None,
+                "collective": collective}
 
     # ---- e2e: the C-ABI host entry with HOST buffers, H2D + kernel + D2H inside the timed region --
     at = tabs.alias_host

@@ -220,6 +220,21 @@ NRW_API int  nrw_fluence_scores_host(nrw_engine* e,
                              int64_t* score_host, unsigned long long* counters_host,
                              void* stream);
 
+/* The path's one collective over peer memory (no NCCL): out[i] = sum over ranks q of
+ * peer_bufs[q][offset + i].  peer_bufs_dev / peer_flags_dev are DEVICE arrays of `world` pointers:
+ * every rank's score buffer (int64) and flag array (uint64[world], zero-initialised) as mapped into
+ * this process (symmetric memory / CUDA IPC; nrw/dist.py uses torch's symmetric-memory allocator).
+ * The kernel publishes `epoch` (> 0, increasing by one per call on every rank) to all peers, waits
+ * for theirs, then reads and sums.  Alternate `offset` between two buffers per epoch: a buffer may be
+ * rewritten once the NEXT call has been enqueued; zero_offset >= 0 makes the kernel zero this rank's
+ * own buffer at that offset after the wait (the buffer of the next step), -1 leaves it.  *err_flag (device int) is set to 1 if a peer does
+ * not arrive within 5 s.  Replaces the all-reduce a multi-process run(args) of
+ * fluence_mini_app.py:397-438 needs once per solve. */
+NRW_API int  nrw_p2p_allreduce_i64(nrw_engine* e, int64_t* out, const void* peer_bufs_dev,
+                                   const void* peer_flags_dev, int64_t offset, int64_t zero_offset,
+                                   int64_t n, int32_t rank, int32_t world, uint64_t epoch,
+                                   int32_t* err_flag, void* stream);
+
 /* Roofline denominators measured on the engine's device at the walk's own launch geometry (one
  * 1024-thread CTA per SM): kind 0 = random atomicAdd on a per-CTA shared-memory histogram of n bins,
  * 1 = dependent random 8-byte shared-memory loads from n entries, 2 = dependent random 8-byte loads

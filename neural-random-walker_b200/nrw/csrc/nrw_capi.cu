@@ -9,6 +9,7 @@
 
 #include "common.cuh"
 #include "microbench.cuh"
+#include "p2p_reduce.cuh"
 #include "post.cuh"
 #include "walk_philox.cuh"
 #include "walk_replay.cuh"
@@ -39,6 +40,7 @@ struct nrw_engine {
     int device;
     int n_sms;
     int max_smem;
+    int clock_khz;                   // SM clock (cached: the attribute query costs ~1 ms per call)
     unsigned long long* work_next;   // device counter the warps pull walker-id ranges from
     // grow-only staging buffers of nrw_fluence_scores_host
     void* d_rowinfo; size_t cap_rowinfo;
@@ -69,6 +71,7 @@ extern "C" int nrw_create(int device, nrw_engine** out) {
     e->device = device;
     e->n_sms = prop.multiProcessorCount;
     e->max_smem = (int)prop.sharedMemPerBlockOptin;
+    e->clock_khz = prop.clockRate > 0 ? prop.clockRate : 2000000;
     CUDA_TRY(cudaMalloc(&e->work_next, sizeof(unsigned long long)));
     CUDA_TRY(cudaMalloc(&e->d_counters, NRW_N_COUNTERS * sizeof(unsigned long long)));
     *out = e;
@@ -502,6 +505,26 @@ extern "C" int nrw_fluence_scores_host(nrw_engine* e, int32_t n_rows, int32_t n_
         CUDA_TRY(cudaMemcpyAsync(counters_host, e->d_counters, NRW_N_COUNTERS * sizeof(unsigned long long),
                                  cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaStreamSynchronize(st));
+    return NRW_OK;
+}
+
+// ---- the path's collective over peer memory ------------------------------------------------------
+extern "C" int nrw_p2p_allreduce_i64(nrw_engine* e, int64_t* out, const void* peer_bufs_dev,
+                                     const void* peer_flags_dev, int64_t offset, int64_t zero_offset,
+                                     int64_t n, int32_t rank, int32_t world, uint64_t epoch,
+                                     int32_t* err_flag, void* stream) {
+    if (!e || !out || !peer_bufs_dev || !peer_flags_dev || !err_flag || n <= 0 || offset < 0 || world < 1 ||
+        world > 64 || rank < 0 || rank >= world || epoch == 0)
+        return fail(NRW_EINVAL, "nrw_p2p_allreduce_i64: bad argument");
+    CUDA_TRY(cudaSetDevice(e->device));
+    long long grid = (n + P2P_THREADS - 1) / P2P_THREADS;
+    if (grid > 16) grid = 16;                                    // 80 KB per peer: latency-, not bandwidth-bound
+    const long long timeout_cycles = (long long)e->clock_khz * 1000ll * 5ll;   // 5 s without a peer: give up
+    p2p_allreduce_i64_kernel<<<(int)grid, P2P_THREADS, 0, (cudaStream_t)stream>>>(
+        (long long*)out, (const long long* const*)peer_bufs_dev, (unsigned long long* const*)peer_flags_dev,
+        (long long)offset, (long long)zero_offset, (long long)n, rank, world, (unsigned long long)epoch,
+        timeout_cycles, err_flag);
+    CUDA_TRY(cudaGetLastError());
     return NRW_OK;
 }
 

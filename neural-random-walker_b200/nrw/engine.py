@@ -67,7 +67,7 @@ _lib = None
 EXPORTS = ("nrw_abi_version", "nrw_last_error", "nrw_create", "nrw_destroy", "nrw_device_info",
            "nrw_build_cum", "nrw_walk_philox", "nrw_walk_philox_plan", "nrw_walk_replay",
            "nrw_assemble_events", "nrw_expand_events", "nrw_expand_counts",
-           "nrw_fluence_scores_host", "nrw_microbench")
+           "nrw_fluence_scores_host", "nrw_microbench", "nrw_p2p_allreduce_i64")
 
 
 def load_library():
@@ -98,6 +98,7 @@ def load_library():
     lib.nrw_fluence_scores_host.argtypes = [vp, i32, i32, i32, vp, vp, i32, vp, vp, i64, i64, u64,
                                             i32, C.POINTER(dbl * 4), vp, vp, vp]
     lib.nrw_microbench.argtypes = [vp, i32, i32, i32, vp, vp, vp, vp]
+    lib.nrw_p2p_allreduce_i64.argtypes = [vp, vp, vp, vp, i64, i64, i64, i32, i32, u64, vp, vp]
     for name in EXPORTS:
         fn = getattr(lib, name)
         if name != "nrw_last_error":
@@ -323,8 +324,14 @@ class Engine:
         cv = np.zeros(4) if class_value is None else np.asarray(class_value, dtype=np.float64).copy()
         cv = identity_weights_if_equivalent(cv, tables.max_class)
         w.class_value = (C.c_double * 4)(*cv.tolist())
-        if score:
-            res.score = torch.zeros(n_starts, dtype=torch.int64, device=self.device)
+        if score is not None and score is not False:
+            if score is True:
+                res.score = torch.zeros(n_starts, dtype=torch.int64, device=self.device)
+            else:                                   # caller's buffer (e.g. symmetric memory, nrw/dist.py)
+                if (score.dtype != torch.int64 or score.numel() != n_starts or not score.is_contiguous()
+                        or score.device != self.device):
+                    raise ValueError("score buffer must be a contiguous int64[n_starts] tensor on the engine's device")
+                res.score = score
             w.score = _ptr(res.score)
             if score_sq:
                 res.score_sq = torch.zeros(n_starts, dtype=torch.float64, device=self.device)

@@ -57,3 +57,16 @@ def test_simple_flux_cli_two_ranks_equals_one(tmp_path):
     one = app.run(a)
     got = np.genfromtxt(str(tmp_path / "r2.csv"), delimiter=",")
     assert got.shape == (2, 1002) and np.array_equal(got, one)
+
+
+@pytest.mark.skipif(not _two_gpus(), reason="needs 2 GPUs")
+@pytest.mark.parametrize("p2p,n", [("1", "10000"), ("1", "4097"), ("0", "10000")])
+def test_p2p_score_allreduce_equals_nccl(p2p, n):
+    """nrw.dist.ScoreAllReduce: the one-kernel reduction over NVLink peer memory (and its NCCL
+    fall-back) equals dist.all_reduce over 25 back-to-back epochs on both score buffers."""
+    worker = os.path.join(os.path.dirname(os.path.abspath(__file__)), "p2p_reduce_worker.py")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+           "--master-addr", "127.0.0.1", "--master-port", str(29641 + int(n) % 7 + (0 if p2p == "1" else 10)), worker]
+    env = dict(os.environ, NRW_P2P_REDUCE=p2p, NRW_TEST_N=n)
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, env=env)
+    assert r.returncode == 0 and "p2p_reduce_worker ok p2p=%s" % (p2p == "1") in r.stdout, (r.stdout[-1500:], r.stderr[-3000:])
