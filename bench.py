@@ -291,6 +291,10 @@ def run_ours(args):
     for _ in range(max(args.warmup, 3)):
         step()
     barrier()
+    if red is not None and not red.settle():                     # a rank timed out: NCCL from here on
+        for _ in range(3):
+            step()
+        barrier()
     steps_per_launch = int(res.counters.cpu()[0].item())          # identical every step (same seed)
 
     evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))

@@ -149,6 +149,20 @@ class ScoreAllReduce:
                                              self._err.data_ptr(), e.stream))
         return self.out
 
+    def settle(self) -> bool:
+        """Collective: after some warm-up reductions, agree on whether the peer-memory path works on
+        every rank (no time-out anywhere); if not, all ranks switch to NCCL for good.  Returns p2p."""
+        if self.world > 1 and self.p2p:
+            import torch.distributed as dist
+            bad = self._err.clone()
+            dist.all_reduce(bad, op=dist.ReduceOp.MAX)
+            if int(bad.item()) != 0:
+                self.p2p = False
+                self._err.zero_()
+                self._bufs.zero_()
+                self.epoch = 0
+        return self.p2p
+
     def check(self):
         """Synchronises; raises if a peer did not arrive at some reduce()."""
         if self.p2p and int(self._err.item()) != 0:
