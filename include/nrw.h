@@ -130,13 +130,17 @@ typedef struct nrw_walk {
     const double* time_weight;      /* [nt] or NULL                                      */
 
     /* occupancy histogram over nodes, all starts together, steps 1 <= t <= nt-2
-     * (per-block shared-memory histogram when it fits, merged once per block).          */
+     * (per-block shared-memory histogram when it fits, merged once per block).  The per-block
+     * bins are 32-bit: one launch must put fewer than 2^32 tallies on one node from one block
+     * (>= 6e11 walker-steps on a single node per launch on 148 SMs); longer runs are split by
+     * walker-id range (walker_lo / walker_hi) -- node_hist accumulates across launches.     */
     unsigned long long* node_hist;  /* [n_rows] or NULL                                  */
 
     /* time-resolved counts == tempdata (fluence_mini_app.py:227,245): group gidx of a
      * walker is its start index s if count_per_start else 0;
      * count_tn[(gidx * t_cap + t) * n_rows + k] += 1 for 1 <= t < min(nt, t_cap).
-     * (t = 0 is the initial condition and is filled by nrw_expand_*).                   */
+     * (t = 0 is the initial condition and is filled by nrw_expand_*).  Bins are 32-bit:
+     * fewer than 2^32 walkers per group and launch.                                      */
     uint32_t* count_tn;             /* or NULL                                           */
     int32_t  t_cap;
     int32_t  count_per_start;

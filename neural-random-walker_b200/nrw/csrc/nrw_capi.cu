@@ -72,8 +72,12 @@ extern "C" int nrw_create(int device, nrw_engine** out) {
     e->n_sms = prop.multiProcessorCount;
     e->max_smem = (int)prop.sharedMemPerBlockOptin;
     e->clock_khz = prop.clockRate > 0 ? prop.clockRate : 2000000;
-    CUDA_TRY(cudaMalloc(&e->work_next, sizeof(unsigned long long)));
-    CUDA_TRY(cudaMalloc(&e->d_counters, NRW_N_COUNTERS * sizeof(unsigned long long)));
+    cudaError_t err = cudaMalloc(&e->work_next, sizeof(unsigned long long));
+    if (err == cudaSuccess) err = cudaMalloc(&e->d_counters, NRW_N_COUNTERS * sizeof(unsigned long long));
+    if (err != cudaSuccess) {
+        nrw_destroy(e);                                   // frees whatever was allocated
+        return fail(NRW_ECUDA, "nrw_create: cudaMalloc failed: %s", cudaGetErrorString(err));
+    }
     *out = e;
     return NRW_OK;
 }
@@ -175,6 +179,11 @@ struct WalkPlan {
     X(TAB_CDF, 1) X(TAB_CDF, 3) X(TAB_CDF, 8) X(TAB_CDF, 9) X(TAB_CDF, 16) X(TAB_CDF, 32)
 
 static int align16(int x) { return (x + 15) & ~15; }
+// table sizes in bytes, clamped so that tables far beyond any shared memory cannot wrap an int
+static int table_bytes(long long n, int elem) {
+    const long long b = (n * elem + 15) & ~15ll;
+    return b > (1ll << 29) ? (1 << 29) : (int)b;
+}
 
 static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, WalkPlan* plan) {
     if (!e || !t || !w) return fail(NRW_EINVAL, "nrw_walk_philox: NULL argument");
@@ -225,6 +234,8 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
     }
     p.counters = w->counters; p.work_next = e->work_next;
     if (w->count_tn && w->t_cap < 1) return fail(NRW_EINVAL, "nrw_walk_philox: t_cap=%d", w->t_cap);
+    if (w->count_tn && w->walker_hi - w->walker_lo >= (1ll << 32))
+        return fail(NRW_EINVAL, "nrw_walk_philox: count_tn bins are 32-bit; walk fewer than 2^32 ids per launch");
 
     // table location
     int smem = 16, tab;
@@ -240,14 +251,15 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
         } else if (t->alias_layout == NRW_ALIAS_COMPACT) {
             if (t->n_alias > (1 << 15))
                 return fail(NRW_EINVAL, "nrw_walk_philox: compact layout holds <= 2^15 alias entries");
-            const int ab = align16(t->n_alias * 8), rb = align16(t->n_rows * 8);
+            const int ab = table_bytes(t->n_alias, 8), rb = table_bytes(t->n_rows, 8);
             // factored row descriptors (fluence-structured meshes): taken when the descriptor table
             // does not fit shared memory but the three small tables do; NRW_TAB=hyb / fac overrides
             const bool have_fac = t->fac_dir && t->fac_tail && t->fac_cls && t->fac_period > 1 &&
                                   t->fac_cells > 0 && t->fac_n_tail == t->n_rows - t->n_live &&
                                   (long long)t->fac_period * t->fac_cells == t->n_live;
-            const int fb = have_fac ? align16(t->fac_period * 8) + align16(t->fac_n_tail * 8) +
-                                      align16(((t->n_live + 15) / 16) * 4) : 0;
+            const long long fbl = have_fac ? (long long)table_bytes(t->fac_period, 8) + table_bytes(t->fac_n_tail, 8) +
+                                             table_bytes((t->n_live + 15) / 16, 4) : 0;
+            const int fb = fbl > (1ll << 29) ? (1 << 29) : (int)fbl;
             const char* tab_env = getenv("NRW_TAB");
             const bool force_fac = tab_env && strcmp(tab_env, "fac") == 0, no_fac = tab_env && strcmp(tab_env, "hyb") == 0;
             if (force_fac && !(have_fac && 16 + ab + fb <= e->max_smem))
@@ -281,7 +293,7 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
     int tl = 0;
     if (w->score) tl |= TL_SCORE | (w->time_weight ? TL_TW : 0);
     if (w->node_hist) {
-        const int hb = align16(t->n_rows * 4);
+        const int hb = table_bytes(t->n_rows, 4);
         if (tab_compact(tab) && smem + hb <= e->max_smem) {
             tl |= TL_HIST_S; p.sm_hist = smem; smem += hb;
         } else {
@@ -466,7 +478,7 @@ extern "C" int nrw_fluence_scores_host(nrw_engine* e, int32_t n_rows, int32_t n_
         return fail(NRW_EINVAL, "nrw_fluence_scores_host: bad argument");
     cudaStream_t st = (cudaStream_t)stream;
     CUDA_TRY(cudaSetDevice(e->device));
-    const size_t rb = (size_t)align16(n_rows * 8), ab = (size_t)align16(n_alias * 8);
+    const size_t rb = ((size_t)n_rows * 8 + 15) & ~(size_t)15, ab = ((size_t)n_alias * 8 + 15) & ~(size_t)15;
     int rc;
     if ((rc = grow(&e->d_rowinfo, &e->cap_rowinfo, rb))) return rc;
     if ((rc = grow(&e->d_alias, &e->cap_alias, ab))) return rc;
@@ -531,7 +543,7 @@ extern "C" int nrw_p2p_allreduce_i64(nrw_engine* e, int64_t* out, const void* pe
 // ---- roofline denominators ----------------------------------------------------------------------
 extern "C" int nrw_microbench(nrw_engine* e, int32_t kind, int32_t n, int32_t iters, const void* table,
                               unsigned long long* hist, unsigned long long* scratch, void* stream) {
-    if (!e || n <= 0 || iters <= 0 || !scratch) return fail(NRW_EINVAL, "nrw_microbench: bad argument");
+    if (!e || n <= 0 || n > (1 << 26) || iters <= 0 || !scratch) return fail(NRW_EINVAL, "nrw_microbench: bad argument");
     cudaStream_t st = (cudaStream_t)stream;
     CUDA_TRY(cudaSetDevice(e->device));
     const int grid = e->n_sms;

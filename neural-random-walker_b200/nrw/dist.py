@@ -53,12 +53,6 @@ def shard_range(total: int, rank: int, world_size: int, align: int = 1):
     return int(lo), int(hi)
 
 
-def interleave_starts(n_starts: int, world_size: int):
-    """Order of start indices that balances the ~50 % instant-exit start nodes across contiguous
-    id shards: not needed when every rank takes an id range of EVERY start (see shard_by_start)."""
-    return list(range(n_starts))
-
-
 def allreduce_sum_(tensors):
     """In-place sum over ranks of each tensor (int64 / float64); the single collective of the path."""
     import torch.distributed as dist
