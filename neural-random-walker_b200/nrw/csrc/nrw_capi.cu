@@ -14,6 +14,7 @@
 #include "walk_philox.cuh"
 #include "walk_replay.cuh"
 #include "walk_score.cuh"
+#include "walk_dense.cuh"
 
 #include <cstdlib>
 
@@ -179,6 +180,9 @@ struct WalkPlan {
     X(TAB_CDF, 1) X(TAB_CDF, 3) X(TAB_CDF, 8) X(TAB_CDF, 9) X(TAB_CDF, 16) X(TAB_CDF, 32)
 
 static int align16(int x) { return (x + 15) & ~15; }
+#ifndef NRW_DENSE_DEFAULT
+#define NRW_DENSE_DEFAULT false      // walk_dense.cuh is opt-in (NRW_K1S=dense)
+#endif
 // table sizes in bytes, clamped so that tables far beyond any shared memory cannot wrap an int
 static int table_bytes(long long n, int elem) {
     const long long b = (n * elem + 15) & ~15ll;
@@ -368,7 +372,25 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
             while (p.range > 32 && p.range * (long long)w->nt * maxw >= (1ll << 31)) p.range = ((p.range / 2) / 32) * 32;
             // two CTAs of 768 threads per SM when the tables leave room (NRW_CPS=1 forces one CTA)
             const char* cps_env = getenv("NRW_CPS");
-            const int cps = (plan->smem <= 112 * 1024 && !(cps_env && strcmp(cps_env, "1") == 0)) ? 2 : 1;
+            const bool cps1_forced = cps_env && strcmp(cps_env, "1") == 0;
+            int cps = (plan->smem <= 112 * 1024 && !cps1_forced) ? 2 : 1;
+            // dense step batches (walk_dense.cuh): score-only walks on shared-memory tables; needs 2 KB of
+            // shared memory per warp for the survivor rings.  NRW_K1S=dense opts in, NRW_K1S=paired forces
+            // the per-lane kernel above
+            bool dense = false;
+            {
+                const char* k1s_env = getenv("NRW_K1S");
+                // by default only where segments are long enough to keep the batches full: >= 512 ids per
+                // range and per start node on average (short segments spend their time draining the rings)
+                const bool big = n >= 512ll * e->n_sms * 32 * 8 && n >= 512ll * w->n_starts;
+                const bool want = k1s_env ? strcmp(k1s_env, "dense") == 0 : (NRW_DENSE_DEFAULT && big);
+                if (want && det && !hist && tab == TAB_SMEM) {
+                    const int q0 = align16(plan->smem);
+                    if (q0 + 24 * DQ_BYTES_PER_WARP <= 112 * 1024 && !cps1_forced) { dense = true; cps = 2; }
+                    else if (q0 + 32 * DQ_BYTES_PER_WARP <= e->max_smem) { dense = true; cps = 1; }
+                    if (dense) { p.sm_queue = q0; plan->smem = q0 + (cps == 2 ? 24 : 32) * DQ_BYTES_PER_WARP; }
+                }
+            }
 #define Y(TAB, IDW, DET, CPS)                                                       \
     if (tab == TAB && idw == IDW && det == DET && cps == CPS) {                     \
         if (hist) {                                                                 \
@@ -384,6 +406,12 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
             Y2(TAB_SMEM, true, false) Y2(TAB_SMEM, false, false) Y2(TAB_HYB, true, false) Y2(TAB_HYB, false, false)
             Y2(TAB_FAC, true, true) Y2(TAB_FAC, false, true) Y2(TAB_FAC, true, false) Y2(TAB_FAC, false, false)
 #undef Y2
+            if (dense) {
+                if (idw && cps == 1) { plan->fn = (const void*)walk_dense_kernel<true, 1>; plan->name = "walk_dense<TAB_SMEM,true,cps=1>"; }
+                if (idw && cps == 2) { plan->fn = (const void*)walk_dense_kernel<true, 2>; plan->name = "walk_dense<TAB_SMEM,true,cps=2>"; }
+                if (!idw && cps == 1) { plan->fn = (const void*)walk_dense_kernel<false, 1>; plan->name = "walk_dense<TAB_SMEM,false,cps=1>"; }
+                if (!idw && cps == 2) { plan->fn = (const void*)walk_dense_kernel<false, 2>; plan->name = "walk_dense<TAB_SMEM,false,cps=2>"; }
+            }
             if (cps == 2) {
                 plan->block = 768;
                 long long g2 = (n + 767) / 768;

@@ -59,6 +59,7 @@ struct WalkParams {
     int fac_period, fac_cells, fac_n_tail, fac_shift;
     uint32_t fac_magic, fac_exit_w0, fac_exit_base;
     int sm_fdir, sm_ftail, sm_fcls;
+    int sm_queue;                                // walk_dense.cuh: per-warp survivor rings
 };
 
 // Row descriptor (w0, base) of row k derived instead of loaded (TAB_FAC): the direction table gives
