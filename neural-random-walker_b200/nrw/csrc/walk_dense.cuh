@@ -112,12 +112,17 @@ walk_dense_kernel(const __grid_constant__ WalkParams p) {
         }
         return true;
     };
+    // Ring heads / tails are monotone BYTE counters (16 per entry); an entry's offset is counter mod 1 KB.
     // survivors of a batch go to the back of ring q, in lane order
+    auto ring_at = [](uint4* q, uint32_t byte_pos) -> uint4* {
+        return reinterpret_cast<uint4*>(reinterpret_cast<unsigned char*>(q) + (byte_pos & (DQ_ENTRIES * 16 - 16)));
+    };
     auto push = [&](uint4* q, uint32_t& tail, bool alive, uint32_t c0, uint32_t w1, int k, int t) {
         const unsigned b = __ballot_sync(NRW_FULL_MASK, alive);
-        if (alive) q[(tail + (uint32_t)__popc(b & lt_mask)) & (DQ_ENTRIES - 1)] = make_uint4(c0, w1, (uint32_t)k, (uint32_t)t);
-        tail += (uint32_t)__popc(b);
+        if (alive) *ring_at(q, tail + ((uint32_t)__popc(b & lt_mask) << 4)) = make_uint4(c0, w1, (uint32_t)k, (uint32_t)t);
+        tail += (uint32_t)__popc(b) << 4;
     };
+    const uint32_t lane16 = (uint32_t)lane << 4;
 
     while (true) {
         // ---- next id range of the warp (one atomic per range) ---------------------------------------
@@ -173,57 +178,65 @@ walk_dense_kernel(const __grid_constant__ WalkParams p) {
             if (t_last >= 2) x += weight_of(row_detcls(srow.x)) * k;     // t = nt-1 is outside the sum
             nst += k;
         } else {
-            uint32_t h1 = 0, t1 = 0, h0 = 0, t0 = 0;         // ring heads / tails (monotone; index mod 64)
+            uint32_t h1 = 0, t1 = 0, h0 = 0, t0 = 0;         // ring heads / tails in bytes (monotone; offset mod 1 KB)
             uint32_t fresh = cur;
-            while (true) {
-                const uint32_t n1 = t1 - h1, n0 = t0 - h0;
-                if (n1 >= 32u || (n0 < 32u && fresh >= seg_end && n1 != 0u)) {
-                    // ---- Q1 batch: the even step of the pair, from the stored word ------------------
-                    const uint32_t cnt = min(n1, 32u);
-                    const bool act = (uint32_t)lane < cnt;
-                    bool alive = false;
-                    uint32_t c0 = 0; int knew = 0, tn = 0;
-                    if (act) {
-                        const uint4 e = q1[(h1 + (uint32_t)lane) & (DQ_ENTRIES - 1)];
-                        const uint2 row = rowinfo_s[e.z];
-                        c0 = e.x; tn = (int)e.w + 1;
-                        alive = step(row.x, row.y, e.y, (int)e.w, knew);
-                    }
-                    h1 += cnt;
-                    push(q0, t0, alive, c0, 0u, knew, tn);
-                } else if (n0 >= 32u || (fresh >= seg_end && n0 != 0u)) {
-                    // ---- Q0 batch: the next Philox call, then the odd step -----------------------------
-                    const uint32_t cnt = min(n0, 32u);
-                    const bool act = (uint32_t)lane < cnt;
-                    bool alive = false;
-                    uint32_t c0 = 0, w1 = 0; int knew = 0, tn = 0;
-                    if (act) {
-                        const uint4 e = q0[(h0 + (uint32_t)lane) & (DQ_ENTRIES - 1)];
-                        const uint2 row = rowinfo_s[e.z];
-                        c0 = e.x; tn = (int)e.w + 1;
-                        const uint2 r = philox2x32_10_rk(c0, chi | (uint32_t)tn, p);
-                        w1 = r.y;
-                        alive = step(row.x, row.y, r.x, (int)e.w, knew);
-                    }
-                    h0 += cnt;
-                    push(q1, t1, alive, c0, w1, knew, tn);
-                } else if (fresh < seg_end) {
-                    // ---- fresh batch: the next <= 32 ids, first call (t = 0), odd step on the start row
-                    const uint32_t cnt = min(seg_end - fresh, 32u);
-                    const bool act = (uint32_t)lane < cnt;
-                    bool alive = false;
-                    const uint32_t c0 = c0_first + (fresh - cur) + (uint32_t)lane;
-                    uint32_t w1 = 0; int knew = 0;
-                    if (act) {
-                        const uint2 r = philox2x32_10_rk(c0, chi | 1u, p);
-                        w1 = r.y;
-                        alive = step(srow.x, srow.y, r.x, 0, knew);
-                    }
-                    fresh += cnt;
-                    push(q1, t1, alive, c0, w1, knew, 1);
-                } else {
-                    break;                                   // segment done, rings empty
+            // The three batch kinds; FULL batches (all 32 lanes) are the steady state and carry no lane
+            // predicate, partial ones only occur at the end of a segment.
+            // Q1 batch: the even step of the pair, from the stored word; survivors -> Q0
+            auto q1_batch = [&](auto full, uint32_t cnt) {
+                constexpr bool FULL = decltype(full)::value;
+                bool alive = false;
+                uint32_t c0 = 0; int knew = 0, tn = 0;
+                if (FULL || (uint32_t)lane < cnt) {
+                    const uint4 e = *ring_at(q1, h1 + lane16);
+                    const uint2 row = rowinfo_s[e.z];
+                    c0 = e.x; tn = (int)e.w + 1;
+                    alive = step(row.x, row.y, e.y, (int)e.w, knew);
                 }
+                h1 += cnt << 4;
+                push(q0, t0, alive, c0, 0u, knew, tn);
+            };
+            // Q0 batch: the next Philox call, then the odd step; survivors -> Q1 with word 1 of the call
+            auto q0_batch = [&](auto full, uint32_t cnt) {
+                constexpr bool FULL = decltype(full)::value;
+                bool alive = false;
+                uint32_t c0 = 0, w1 = 0; int knew = 0, tn = 0;
+                if (FULL || (uint32_t)lane < cnt) {
+                    const uint4 e = *ring_at(q0, h0 + lane16);
+                    const uint2 row = rowinfo_s[e.z];
+                    c0 = e.x; tn = (int)e.w + 1;
+                    const uint2 r = philox2x32_10_rk(c0, chi | (uint32_t)tn, p);
+                    w1 = r.y;
+                    alive = step(row.x, row.y, r.x, (int)e.w, knew);
+                }
+                h0 += cnt << 4;
+                push(q1, t1, alive, c0, w1, knew, tn);
+            };
+            // fresh batch: the next <= 32 ids, first call (t = 0), odd step on the start row; survivors -> Q1
+            auto fresh_batch = [&](auto full, uint32_t cnt) {
+                constexpr bool FULL = decltype(full)::value;
+                bool alive = false;
+                const uint32_t c0 = c0_first + (fresh - cur) + (uint32_t)lane;
+                uint32_t w1 = 0; int knew = 0;
+                if (FULL || (uint32_t)lane < cnt) {
+                    const uint2 r = philox2x32_10_rk(c0, chi | 1u, p);
+                    w1 = r.y;
+                    alive = step(srow.x, srow.y, r.x, 0, knew);
+                }
+                fresh += cnt;
+                push(q1, t1, alive, c0, w1, knew, 1);
+            };
+            // Schedule: a full ring is popped first (Q1 before Q0), then fresh ids; partial batches drain
+            // what is left.  Pushes onto Q1 (Q0 / fresh batches) happen only while Q1 holds < 32, pushes
+            // onto Q0 (Q1 batches) only while Q0 holds < 32: no ring ever holds more than 63 walkers.
+            while (true) {
+                if (t1 - h1 >= 512u)          q1_batch(std::true_type{}, 32u);
+                else if (t0 - h0 >= 512u)     q0_batch(std::true_type{}, 32u);
+                else if (seg_end - fresh >= 32u) fresh_batch(std::true_type{}, 32u);
+                else if (seg_end != fresh)    fresh_batch(std::false_type{}, seg_end - fresh);
+                else if (t1 != h1)            q1_batch(std::false_type{}, (t1 - h1) >> 4);
+                else if (t0 != h0)            q0_batch(std::false_type{}, (t0 - h0) >> 4);
+                else break;                                  // segment done, rings empty
                 __syncwarp();                                // ring writes visible to the lanes that pop them
             }
         }
