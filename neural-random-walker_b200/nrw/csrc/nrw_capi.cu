@@ -14,7 +14,6 @@
 #include "walk_philox.cuh"
 #include "walk_replay.cuh"
 #include "walk_score.cuh"
-#include "walk_dense.cuh"
 
 #include <cstdlib>
 
@@ -180,9 +179,6 @@ struct WalkPlan {
     X(TAB_CDF, 1) X(TAB_CDF, 3) X(TAB_CDF, 8) X(TAB_CDF, 9) X(TAB_CDF, 16) X(TAB_CDF, 32)
 
 static int align16(int x) { return (x + 15) & ~15; }
-#ifndef NRW_DENSE_DEFAULT
-#define NRW_DENSE_DEFAULT false      // walk_dense.cuh is opt-in (NRW_K1S=dense)
-#endif
 // table sizes in bytes, clamped so that tables far beyond any shared memory cannot wrap an int
 static int table_bytes(long long n, int elem) {
     const long long b = (n * elem + 15) & ~15ll;
@@ -372,25 +368,7 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
             while (p.range > 32 && p.range * (long long)w->nt * maxw >= (1ll << 31)) p.range = ((p.range / 2) / 32) * 32;
             // two CTAs of 768 threads per SM when the tables leave room (NRW_CPS=1 forces one CTA)
             const char* cps_env = getenv("NRW_CPS");
-            const bool cps1_forced = cps_env && strcmp(cps_env, "1") == 0;
-            int cps = (plan->smem <= 112 * 1024 && !cps1_forced) ? 2 : 1;
-            // dense step batches (walk_dense.cuh): score-only walks on shared-memory tables; needs 2 KB of
-            // shared memory per warp for the survivor rings.  NRW_K1S=dense opts in, NRW_K1S=paired forces
-            // the per-lane kernel above
-            bool dense = false;
-            {
-                const char* k1s_env = getenv("NRW_K1S");
-                // by default only where segments are long enough to keep the batches full: >= 512 ids per
-                // range and per start node on average (short segments spend their time draining the rings)
-                const bool big = n >= 512ll * e->n_sms * 32 * 8 && n >= 512ll * w->n_starts;
-                const bool want = k1s_env ? strcmp(k1s_env, "dense") == 0 : (NRW_DENSE_DEFAULT && big);
-                if (want && det && !hist && tab == TAB_SMEM) {
-                    const int q0 = align16(plan->smem);
-                    if (q0 + 24 * DQ_BYTES_PER_WARP <= 112 * 1024 && !cps1_forced) { dense = true; cps = 2; }
-                    else if (q0 + 32 * DQ_BYTES_PER_WARP <= e->max_smem) { dense = true; cps = 1; }
-                    if (dense) { p.sm_queue = q0; plan->smem = q0 + (cps == 2 ? 24 : 32) * DQ_BYTES_PER_WARP; }
-                }
-            }
+            const int cps = (plan->smem <= 112 * 1024 && !(cps_env && strcmp(cps_env, "1") == 0)) ? 2 : 1;
 #define Y(TAB, IDW, DET, CPS)                                                       \
     if (tab == TAB && idw == IDW && det == DET && cps == CPS) {                     \
         if (hist) {                                                                 \
@@ -406,12 +384,6 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
             Y2(TAB_SMEM, true, false) Y2(TAB_SMEM, false, false) Y2(TAB_HYB, true, false) Y2(TAB_HYB, false, false)
             Y2(TAB_FAC, true, true) Y2(TAB_FAC, false, true) Y2(TAB_FAC, true, false) Y2(TAB_FAC, false, false)
 #undef Y2
-            if (dense) {
-                if (idw && cps == 1) { plan->fn = (const void*)walk_dense_kernel<true, 1>; plan->name = "walk_dense<TAB_SMEM,true,cps=1>"; }
-                if (idw && cps == 2) { plan->fn = (const void*)walk_dense_kernel<true, 2>; plan->name = "walk_dense<TAB_SMEM,true,cps=2>"; }
-                if (!idw && cps == 1) { plan->fn = (const void*)walk_dense_kernel<false, 1>; plan->name = "walk_dense<TAB_SMEM,false,cps=1>"; }
-                if (!idw && cps == 2) { plan->fn = (const void*)walk_dense_kernel<false, 2>; plan->name = "walk_dense<TAB_SMEM,false,cps=2>"; }
-            }
             if (cps == 2) {
                 plan->block = 768;
                 long long g2 = (n + 767) / 768;
@@ -424,6 +396,37 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
             }
 #undef Y
         }
+    }
+    {   // guided range sizes (fetch_range, walk_philox.cuh): phase 0 = big ranges; the last `tail_ranges` big
+        // ranges per warp of the id space go out in phases of ranges half as long each (two per warp and
+        // phase) down to range_tail ids.  NRW_RANGE_TAIL / NRW_TAIL_RANGES override (0 ranges = one size)
+        const char* rt_env = getenv("NRW_RANGE_TAIL");
+        const char* tr_env = getenv("NRW_TAIL_RANGES");
+        long long rt = rt_env ? atoll(rt_env) : 1024;
+        rt = (rt / 32) * 32;
+        if (rt < 32) rt = 32;
+        if (rt > p.range) rt = p.range;
+        const long long tail_ranges = tr_env ? atoll(tr_env) : 2;
+        const long long warps = (long long)plan->grid * (plan->block / 32);
+        long long tail_ids = tail_ranges <= 0 ? 0 : tail_ranges * p.range * warps;
+        if (tail_ids > n) tail_ids = n;
+        int np = 0;
+        long long start = 0, ticket = 0, r = p.range;
+        while (true) {
+            const bool last = np == NRW_MAX_PHASES - 1 || r <= rt || tail_ids == 0;
+            const long long stop = last ? n : n - tail_ids;         // this phase covers [start, stop)
+            if (stop > start || last) {
+                p.ph_start[np] = start; p.ph_ticket[np] = ticket; p.ph_range[np] = r;
+                ticket += (stop - start + r - 1) / r;
+                start = stop;
+                ++np;
+            }
+            if (last) break;
+            r = std::max(rt, ((r / 2) / 32) * 32);
+            tail_ids /= 2;
+        }
+        p.n_phase = np;
+        p.ph_start[np] = n; p.ph_ticket[np] = ticket;
     }
     if (!plan->fn)
         return fail(NRW_EINVAL, "nrw_walk_philox: tally combination %d is not built for table mode %d "

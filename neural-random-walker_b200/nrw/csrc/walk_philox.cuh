@@ -33,6 +33,7 @@ __host__ __device__ constexpr bool tab_compact(int tab) { return tab == TAB_SMEM
 enum : int { TL_SCORE = 1, TL_TW = 2, TL_HIST_S = 4, TL_HIST_G = 8, TL_CNT_S = 16, TL_CNT_G = 32 };
 
 constexpr int WALK_THREADS = 1024;
+constexpr int NRW_MAX_PHASES = 8;
 
 struct WalkParams {
     int n_rows, n_live, n_alias;
@@ -49,6 +50,10 @@ struct WalkParams {
     uint32_t* count_tn; int t_cap; int per_start; int cnt_bins; int cnt_match;
     unsigned long long* counters;
     unsigned long long* work_next; long long range;
+    // guided range sizes (walk_score.cuh, fetch_range below): phase j hands out ids
+    // [lo + ph_start[j], lo + ph_start[j+1]) in ranges of ph_range[j], tickets ph_ticket[j] .. ph_ticket[j+1]-1
+    int n_phase;
+    long long ph_start[NRW_MAX_PHASES + 1], ph_ticket[NRW_MAX_PHASES + 1], ph_range[NRW_MAX_PHASES];
     // shared-memory carve-up (byte offsets into dynamic smem)
     int sm_rowinfo, sm_alias, sm_hist, sm_cnt;
     // CTA-level cache of hot (t, node) bins in front of the global time-resolved counts: 2^ccache_bits
@@ -59,7 +64,6 @@ struct WalkParams {
     int fac_period, fac_cells, fac_n_tail, fac_shift;
     uint32_t fac_magic, fac_exit_w0, fac_exit_base;
     int sm_fdir, sm_ftail, sm_fcls;
-    int sm_queue;                                // walk_dense.cuh: per-warp survivor rings
 };
 
 // Row descriptor (w0, base) of row k derived instead of loaded (TAB_FAC): the direction table gives
@@ -78,6 +82,52 @@ __device__ __forceinline__ uint2 fac_row(const WalkParams& p, int k) {
     const bool leaves = jn >= (uint32_t)p.fac_cells;
     return make_uint2((leaves ? p.fac_exit_w0 : d.x) | (cls << 30),
                       leaves ? p.fac_exit_base : jn * (uint32_t)p.fac_period);
+}
+
+// Next id range [nb, nb + len) of a warp, or false when the launch's ids are exhausted (walk_score.cuh).
+// Ranges are numbered by TICKETS drawn from one global counter and their sizes are GUIDED: phase 0 hands
+// out big ranges (few fetches), and the tail of the id space goes out in phases of ranges half as long
+// each, two ranges per warp and phase, down to `range_tail` ids -- so that the warps finish together.  With one range size the SM sub-partitions were
+// active for 88 % of the kernel on average: a warp that draws a heavy range last finishes up to one range
+// late (now 96 %).  Small ranges everywhere are no alternative: every fetch idles part of the warp for an
+// iteration and the returning atomics on the one counter serialise in L2 (a launch with 128-id ranges for
+// a quarter of its ids: 0.55 -> 0.96 ms); the guided sizes need ~13 tickets per warp.  (Drawing the next ticket ahead of time
+// was measured and dropped: a warp that holds a range in advance keeps it from warps that run dry first.)
+__device__ __forceinline__ bool fetch_range(const WalkParams& p, int lane, long long& nb, long long& len) {
+    long long t = 0;
+    if (lane == 0) t = (long long)atomicAdd(p.work_next, 1ull);
+    t = __shfl_sync(NRW_FULL_MASK, t, 0);
+    int j = 0;
+#pragma unroll 1
+    while (j < p.n_phase && t >= p.ph_ticket[j + 1]) ++j;
+    if (j >= p.n_phase) return false;
+    const long long a = p.ph_start[j] + (t - p.ph_ticket[j]) * p.ph_range[j];
+    nb = p.lo + a;
+    len = min(p.ph_range[j], p.ph_start[j + 1] - a);
+    return true;
+}
+
+// Start index s with start_prefix[s] <= g < start_prefix[s + 1].  Interpolation guess first -- exact when
+// every start holds the same number of walkers (the fluence solve: M per node), one round trip to L2
+// instead of the log2(n_starts) dependent ones of the bisection that remains the fall-back.
+__device__ __forceinline__ int locate_start(const WalkParams& p, long long g) {
+    const long long* __restrict__ pre = p.start_prefix;
+    const int n = p.n_starts;
+    const long long total = __ldg(pre + n);
+    int s0 = (int)((double)g * (double)n / (double)total);
+    s0 = max(1, min(s0, n - 2));                             // window s0-1 .. s0+1 inside [0, n) when n >= 3
+    if (n >= 3) {
+        const long long a0 = __ldg(pre + s0 - 1), a1 = __ldg(pre + s0), a2 = __ldg(pre + s0 + 1), a3 = __ldg(pre + s0 + 2);
+        if (a1 <= g && g < a2) return s0;
+        if (a0 <= g && g < a1) return s0 - 1;
+        if (a2 <= g && g < a3) return s0 + 1;
+    }
+    int lo_i = 0, hi_i = n;
+    while (hi_i - lo_i > 1) {
+        const int mid = (lo_i + hi_i) >> 1;
+        if (__ldg(pre + mid) <= g) lo_i = mid; else hi_i = mid;
+    }
+    return lo_i;
 }
 
 template <int TAB>

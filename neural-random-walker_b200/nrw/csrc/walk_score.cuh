@@ -148,12 +148,7 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
             if (gnew < e2) { ++s; s_end = e2; found = true; }
         }
         if (!found) {
-            int lo_i = 0, hi_i = p.n_starts;
-            while (hi_i - lo_i > 1) {
-                const int mid = (lo_i + hi_i) >> 1;
-                if (__ldg(p.start_prefix + mid) <= gnew) lo_i = mid; else hi_i = mid;
-            }
-            s = lo_i;
+            s = locate_start(p, gnew);
             s_lo = __ldg(p.start_prefix + s);
             s_end = __ldg(p.start_prefix + s + 1);
         }
@@ -220,14 +215,11 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
             if (!exhausted) {
                 nsteps += nst; nst = 0;
                 if (x >= 0x80000000u) flush_score();       // keeps the 32-bit running score from wrapping
-                long long a = 0;
-                if (lane == 0) a = (long long)atomicAdd(p.work_next, (unsigned long long)p.range);
-                a = __shfl_sync(NRW_FULL_MASK, a, 0);
-                const long long nb = p.lo + a;
-                if (nb >= p.hi) exhausted = true;
+                long long nb = 0, len = 0;
+                if (!fetch_range(p, lane, nb, len)) exhausted = true;
                 else {
                     cur = 0;
-                    end = (uint32_t)min(p.range, p.hi - nb);
+                    end = (uint32_t)len;
                     wwalk += end;
                     sid_base += nb - rbase;
                     rbase = nb;

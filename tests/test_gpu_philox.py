@@ -306,9 +306,6 @@ def k1_env(monkeypatch):
         monkeypatch.delenv("NRW_K1", raising=False)
         monkeypatch.delenv("NRW_DET", raising=False)
         monkeypatch.delenv("NRW_CPS", raising=False)
-        monkeypatch.delenv("NRW_K1S", raising=False)
-        if variant == "dense":
-            monkeypatch.setenv("NRW_K1S", "dense")
         if variant == "fast_cps1":
             monkeypatch.setenv("NRW_CPS", "1")
         if variant == "general":
@@ -318,7 +315,7 @@ def k1_env(monkeypatch):
     return set_variant
 
 
-@pytest.mark.parametrize("variant", ["fast", "fast_cps1", "fast_nodet", "general", "dense"])
+@pytest.mark.parametrize("variant", ["fast", "fast_cps1", "fast_nodet", "general"])
 def test_score_fast_path_bit_exact_all_variants(engine, c1_csr, k1_env, variant):
     """walk_score_kernel and the general kernel produce the same integers as the numpy port:
     identity and packed class weights, ragged starts with the sink and empty starts in the list,
@@ -329,7 +326,7 @@ def test_score_fast_path_bit_exact_all_variants(engine, c1_csr, k1_env, variant)
     _, nc1, _ = _classes(c1_csr, mesh.source_default)                    # classes {0, 1}
     nc3 = (np.arange(c1_csr.n_rows) % 4).astype(np.uint8)                # classes {0, 1, 2, 3}
     nc3[900] = 2                                                         # a weighted sink
-    want = {"general": "walk_philox<", "dense": "walk_dense<TAB_SMEM"}.get(variant, "walk_score<TAB_SMEM")
+    want = "walk_philox<" if variant == "general" else "walk_score<TAB_SMEM"
     starts = np.array([435, 0, 900, 14, 14, 899, 450, 16, 464])
     counts = np.array([3000, 0, 17, 1, 333, 64, 5, 2500, 1200])
     total = int(counts.sum())
@@ -345,7 +342,6 @@ def test_score_fast_path_bit_exact_all_variants(engine, c1_csr, k1_env, variant)
                 assert want in res.kernel, res.kernel
                 if variant != "general":
                     assert (",true," if idw else ",false,") in res.kernel, res.kernel
-                if variant not in ("general", "dense"):
                     assert (",false,cps=" if variant == "fast_nodet" else ",true,cps=") in res.kernel, res.kernel
                     assert res.kernel.endswith("cps=1>" if variant == "fast_cps1" else "cps=2>"), res.kernel
             else:
@@ -395,7 +391,7 @@ def _full_size_scores(engine, k1_env, variants):
     _, nc, _ = _classes(csr, mesh.source_default)
     tabs = engine.upload(csr, node_class=nc)
     out = {}
-    for variant in variants:
+    for variant in ("fast", "fast_nodet", "general"):
         k1_env(variant)
         r = engine.walk(tabs, np.arange(10000), 1000, 30000, 3, score=True, class_value=[0, 1, 0, 0])
         out[variant] = (r.score.cpu().numpy(), r.counters_dict(), r.kernel)
@@ -411,16 +407,7 @@ def test_score_fast_path_equals_general_kernel_at_full_size(engine, k1_env):
         assert out[v][1] == out["general"][1]
 
 
-def test_dense_batches_equal_general_kernel_at_full_size(engine, k1_env):
-    """C5 mesh, 1e7 walkers: walk_dense.cuh (dense step batches, survivor rings) == the general kernel."""
-    out = _full_size_scores(engine, k1_env, ("dense", "general"))
-    assert "walk_dense<TAB_SMEM,true,cps=1>" in out["dense"][2], out["dense"][2]
-    assert np.array_equal(out["dense"][0], out["general"][0])
-    assert out["dense"][1] == out["general"][1]
-
-
-@pytest.mark.parametrize("variants", [("fast", "fast_nodet", "general"), ("dense",)], ids=["paired", "dense"])
-def test_deterministic_rows_on_a_general_graph(engine, k1_env, variants):
+def test_deterministic_rows_on_a_general_graph(engine, k1_env):
     """Single-successor rows of every kind: successor absorbing (folded without a draw), successor
     live (stepped normally), chains of them, a deterministic start, weighted absorbing rows."""
     from nrw import mesh, tables
@@ -445,7 +432,7 @@ def test_deterministic_rows_on_a_general_graph(engine, k1_env, variants):
     tabs = engine.upload(csr, node_class=nc)
     starts = np.array([0, 5, 6, 7, 8, 9, 10, 3, 55, 21])
     counts = np.array([4000, 300, 300, 300, 77, 300, 50, 4000, 9, 2000])
-    for variant in variants:
+    for variant in ("fast", "fast_nodet", "general"):
         k1_env(variant)
         for cv in ([0, 1, 2, 3], [3, 0, 200, 7]):
             for nt in (40, 2, 3, 4):
@@ -454,9 +441,8 @@ def test_deterministic_rows_on_a_general_graph(engine, k1_env, variants):
                 _cmp(res, port, hist=False)
 
 
-@pytest.mark.parametrize("variants", [("fast", "fast_nodet", "general"), ("dense",)], ids=["paired", "dense"])
 @pytest.mark.parametrize("seed", list(range(16)))
-def test_random_graphs_differential(engine, k1_env, seed, variants):
+def test_random_graphs_differential(engine, k1_env, seed):
     """Differential test on random sparse graphs: both kernels == numpy port for random row lengths,
     absorbing rows anywhere, single-successor rows (absorbing and live targets, self loops), random
     classes / weights, ragged start lists, id windows and stream-id bases."""
@@ -495,14 +481,11 @@ def test_random_graphs_differential(engine, k1_env, seed, variants):
         idb = (np.arange(1, n_starts + 1, dtype=np.int64) << 32) - rng.integers(0, np.maximum(counts, 1) + 1)
     port = philox_port.walk_port(csr, starts, counts, nt, seed, alias=tabs.alias_host, class_value=cv,
                                  walker_range=window, start_id_base=idb)
-    for variant in variants:
+    for variant in ("fast", "fast_nodet", "general"):
         k1_env(variant)
         res = engine.walk(tabs, starts, counts, nt, seed, score=True, class_value=cv, walker_range=window,
                           start_id_base=idb)
         _cmp(res, port, hist=False)
-        if variant == "dense":                                 # score-only kernel: the histogram legs are the paired kernel's
-            assert "walk_dense<" in res.kernel or tabs.alias_host.layout != "compact" or "TAB_HYB" in res.kernel, res.kernel
-            continue
         # the same walk with the occupancy histogram (walk_score_hist / general kernel), and histogram only
         res = engine.walk(tabs, starts, counts, nt, seed, score=True, class_value=cv, walker_range=window,
                           start_id_base=idb, node_hist=True)

@@ -27,9 +27,16 @@ def main():
     tabs = eng.upload(csr, node_class=nc)
     starts = np.arange(csr.n_live)
     flush = torch.empty(512 << 20, dtype=torch.uint8, device=eng.device)
-    for tag, env in (("default", {}), ("cps1", {"NRW_CPS": "1"}), ("always_draw", {"NRW_DET": "0"}),
-                     ("general", {"NRW_K1": "general"}), ("dense", {"NRW_K1S": "dense"})):
-        for k in ("NRW_CPS", "NRW_DET", "NRW_K1", "NRW_K1S"):
+    knobs = ("NRW_CPS", "NRW_DET", "NRW_K1", "NRW_RANGE_TAIL", "NRW_TAIL_RANGES")
+    configs = [("default", {}), ("cps1", {"NRW_CPS": "1"}), ("single_range_size", {"NRW_TAIL_RANGES": "0"}),
+               ("always_draw", {"NRW_DET": "0"}), ("general", {"NRW_K1": "general"})]
+    if len(sys.argv) > 3 and sys.argv[3] == "sweep":        # guided range sizes: smallest range x tail share
+        configs = [("single_range_size", {"NRW_TAIL_RANGES": "0"}), ("general_control", {"NRW_K1": "general"})]
+        for rt, tr in ((2048, 2), (1024, 2), (512, 2), (256, 2), (128, 2), (64, 2), (1024, 1), (1024, 3), (512, 1),
+                       (512, 3), (1024, 4)):
+            configs.append(("min%d_x%d" % (rt, tr), {"NRW_RANGE_TAIL": str(rt), "NRW_TAIL_RANGES": str(tr)}))
+    for tag, env in configs:
+        for k in knobs:
             os.environ.pop(k, None)
         os.environ.update(env)
         launch, res = eng.prepare_walk(tabs, starts, M, 30000, seed=1, score=True, class_value=[0, 1, 0, 0])
