@@ -366,9 +366,11 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
                     if (wi > maxw) maxw = wi;
                 }
             while (p.range > 32 && p.range * (long long)w->nt * maxw >= (1ll << 31)) p.range = ((p.range / 2) / 32) * 32;
-            // two CTAs of 768 threads per SM when the tables leave room (NRW_CPS=1 forces one CTA)
+            // one CTA of 1024 threads per SM.  NRW_CPS=2: two CTAs of 768 threads when the tables leave room
+            // (48 instead of 32 warps per SM) -- +1.5 % before the range sizes were guided, 4-40 % slower
+            // since (C1 mesh, 9e5 .. 1.35e8 walkers): more warps draw more tickets for no gain in issue rate
             const char* cps_env = getenv("NRW_CPS");
-            const int cps = (plan->smem <= 112 * 1024 && !(cps_env && strcmp(cps_env, "1") == 0)) ? 2 : 1;
+            const int cps = (plan->smem <= 112 * 1024 && cps_env && strcmp(cps_env, "2") == 0) ? 2 : 1;
 #define Y(TAB, IDW, DET, CPS)                                                       \
     if (tab == TAB && idw == IDW && det == DET && cps == CPS) {                     \
         if (hist) {                                                                 \

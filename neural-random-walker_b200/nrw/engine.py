@@ -186,6 +186,10 @@ class PreparedWalk:
         for t in self.tallies:
             t.zero_()
 
+    def set_seed(self, seed):
+        """Same launch, other Philox key (a fresh, independent set of trajectories)."""
+        self.w.seed = int(seed) & 0xFFFFFFFFFFFFFFFF
+
     def launch_kernel(self):
         e = self.engine
         e._check(e.lib.nrw_walk_philox(e.handle, C.byref(self.tables.struct), C.byref(self.w), e.stream))
@@ -290,7 +294,7 @@ class Engine:
     # ------------------------------------------------------------------ K1
     def _walk_struct(self, tables, start_nodes, start_counts, nt, seed, walker_range, sampler,
                      score, score_sq, class_value, time_weight, node_hist, count_tn, t_cap,
-                     count_per_start, start_id_base=None):
+                     count_per_start, start_id_base=None, counters=None):
         torch = self.torch
         start_nodes = np.asarray(start_nodes, dtype=np.int64).reshape(-1)
         n_starts = len(start_nodes)
@@ -319,7 +323,13 @@ class Engine:
             w.start_id_base = _ptr(keep["id_base"])
         w.seed = int(seed) & 0xFFFFFFFFFFFFFFFF
         w.nt, w.sampler = int(nt), SAMPLER[sampler]
-        res = WalkResult(counters=torch.zeros(NRW_N_COUNTERS, dtype=torch.int64, device=self.device))
+        if counters is None:
+            counters = torch.zeros(NRW_N_COUNTERS, dtype=torch.int64, device=self.device)
+        elif (counters.dtype != torch.int64 or counters.numel() != NRW_N_COUNTERS or not counters.is_contiguous()
+                or counters.device != self.device):
+            raise ValueError("counters buffer must be a contiguous int64[%d] tensor on the engine's device"
+                             % NRW_N_COUNTERS)
+        res = WalkResult(counters=counters)
         w.counters = _ptr(res.counters)
         cv = np.zeros(4) if class_value is None else np.asarray(class_value, dtype=np.float64).copy()
         cv = identity_weights_if_equivalent(cv, tables.max_class)
@@ -375,7 +385,7 @@ class Engine:
         launches K1 again (what bench.py times: no host-side table or descriptor work per step)."""
         args = dict(walker_range=None, sampler="alias", score=False, score_sq=False, class_value=None,
                     time_weight=None, node_hist=False, count_tn=False, t_cap=None, count_per_start=False,
-                    start_id_base=None)
+                    start_id_base=None, counters=None)
         args.update(kw)
         w, res, keep = self._walk_struct(tables, start_nodes, start_counts, nt, seed, **args)
         name = C.create_string_buffer(96)

@@ -17,7 +17,7 @@ from . import dist as _dist
 from . import mesh as _mesh
 from . import tables as _tables
 from .dropin import device_tables, exp_time_weights, resolve_rng
-from .engine import get_engine
+from .engine import COUNTER_NAMES as _COUNTER_NAMES, NRW_N_COUNTERS, get_engine
 
 rw_logger = logging.getLogger("NRW")
 
@@ -47,6 +47,44 @@ def scatter_to_rwsol(per_start: np.ndarray, NS: int, ND: int) -> np.ndarray:
     rwSol = np.zeros((NS - 1, nd1))
     rwSol[posind, aind] = per_start                       # later i overwrite earlier: numpy keeps the last
     return rwSol
+
+
+_fused_cache: dict = {}
+
+
+def _fused_solver(eng, tabs, starts, M, lo_m, hi_m, nt, sampler, cv):
+    """solve(seed) -> pinned int64[n_starts + NRW_N_COUNTERS] host view (scores, then counters) of one fused
+    fluence walk of walkers [lo_m, hi_m) of every start, summed over ranks.  Built once per (tables, M, slice,
+    nt, weights): the start list, the launch descriptor, the tally buffer and its pinned mirror are reused."""
+    import torch
+    key = (id(tabs), M, lo_m, hi_m, int(nt), sampler, tuple(float(x) for x in cv))
+    hit = _fused_cache.get(key)
+    if hit is not None and hit.tabs is tabs:
+        return hit
+    if len(_fused_cache) > 16:
+        _fused_cache.clear()
+    n = len(starts)
+    buf = torch.zeros(n + NRW_N_COUNTERS, dtype=torch.int64, device=eng.device)
+    pinned = torch.empty(n + NRW_N_COUNTERS, dtype=torch.int64).pin_memory()
+    host = pinned.numpy()
+    counts = np.full(n, hi_m - lo_m, dtype=np.int64)
+    id_base = starts.astype(np.int64) * M + lo_m             # the unsharded stream ids (start * M + m)
+    pw, res = eng.prepare_walk(tabs, starts, counts, nt, 0, sampler=sampler, score=buf[:n], class_value=cv,
+                               start_id_base=id_base, counters=buf[n:])
+    rank, world = _dist.world()
+
+    def solve(seed):
+        pw.set_seed(seed)
+        buf.zero_()
+        pw.launch_kernel()
+        if world > 1:
+            _dist.allreduce_sum_([buf])
+        pinned.copy_(buf, non_blocking=True)
+        torch.cuda.current_stream(eng.device).synchronize()
+        return host
+    solve.tabs, solve.kernel, solve.keepalive = tabs, res.kernel, (pw, res, buf, pinned)
+    _fused_cache[key] = solve
+    return solve
 
 
 def solve_fluence(csr: _mesh.TransitionCSR, M: int, nt: int, SigA, dt, v, source=_mesh.source_default,
@@ -95,6 +133,16 @@ def solve_fluence(csr: _mesh.TransitionCSR, M: int, nt: int, SigA, dt, v, source
         tw = exp_time_weights(SigA, dt, nt)
     # every rank walks the same slice of EVERY start's walkers (balanced: starts differ in lifetime)
     lo_m, hi_m = _dist.shard_range(int(M), rank, world)
+    if tw is None and not want_stderr:
+        # the common solve (count hits, no per-walker variance): one prepared launch per (tables, M, nt),
+        # scores and counters in ONE device buffer -- one fill, one launch, one collective, one copy back
+        fs = _fused_solver(eng, tabs, starts, int(M), lo_m, hi_m, nt, sampler, cv)
+        host = fs(seed)
+        score = host[:meshSize].astype(np.float64)
+        c = {k: int(x) for k, x in zip(_COUNTER_NAMES, host[meshSize:].view(np.uint64))}
+        per_start = score * (unit * v * dt) / M
+        return FluenceResult(scatter_to_rwsol(per_start, NS, ND), per_start, c["steps"], "philox",
+                             counters=c, kernel=fs.kernel)
     counts = np.full(meshSize, hi_m - lo_m, dtype=np.int64)
     id_base = starts.astype(np.int64) * int(M) + lo_m
     res = eng.walk(tabs, starts, counts, nt, seed, sampler=sampler, score=True,

@@ -198,6 +198,25 @@ def test_fluence_philox_matches_reference_expectation(engine, c1_csr):
                 assert abs(np.median(ratio) - 1.0) < 0.01 and np.abs(ratio - 1.0).max() < 0.25
 
 
+def test_fused_solve_path_equals_the_general_launch(engine, c1_csr):
+    """solve_fluence's prepared path (one launch descriptor, scores + counters in one buffer, pinned copy
+    back; taken when no per-walker variance is asked for) returns what the per-call path returns, and a
+    re-used descriptor carries nothing over from the previous seed."""
+    from nrw import mesh
+    from nrw.fluence import solve_fluence
+    args = (c1_csr, 700, 64, 0, C1["dt"], C1["v"])
+    for source in (mesh.source_default, mesh.source_paper):
+        ref = {seed: solve_fluence(*args, source=source, rng="philox", seed=seed, want_stderr=True) for seed in (3, 4)}
+        for seed in (3, 4, 3):
+            res = solve_fluence(*args, source=source, rng="philox", seed=seed)
+            assert res.stderr is None and "walk_score<" in res.kernel
+            assert np.array_equal(res.per_start, ref[seed].per_start)
+            assert np.array_equal(res.rwSol, ref[seed].rwSol)
+            assert res.walker_steps == ref[seed].walker_steps
+            for k in ("steps", "exits", "survivors", "walkers"):
+                assert res.counters[k] == ref[seed].counters[k], k
+
+
 def test_fluence_philox_time_weighted_matches_expectation(engine, c1_csr):
     from nrw import mesh
     from nrw.fluence import solve_fluence
@@ -306,8 +325,8 @@ def k1_env(monkeypatch):
         monkeypatch.delenv("NRW_K1", raising=False)
         monkeypatch.delenv("NRW_DET", raising=False)
         monkeypatch.delenv("NRW_CPS", raising=False)
-        if variant == "fast_cps1":
-            monkeypatch.setenv("NRW_CPS", "1")
+        if variant == "fast_cps2":
+            monkeypatch.setenv("NRW_CPS", "2")
         if variant == "general":
             monkeypatch.setenv("NRW_K1", "general")
         elif variant == "fast_nodet":
@@ -315,7 +334,7 @@ def k1_env(monkeypatch):
     return set_variant
 
 
-@pytest.mark.parametrize("variant", ["fast", "fast_cps1", "fast_nodet", "general"])
+@pytest.mark.parametrize("variant", ["fast", "fast_cps2", "fast_nodet", "general"])
 def test_score_fast_path_bit_exact_all_variants(engine, c1_csr, k1_env, variant):
     """walk_score_kernel and the general kernel produce the same integers as the numpy port:
     identity and packed class weights, ragged starts with the sink and empty starts in the list,
@@ -343,7 +362,7 @@ def test_score_fast_path_bit_exact_all_variants(engine, c1_csr, k1_env, variant)
                 if variant != "general":
                     assert (",true," if idw else ",false,") in res.kernel, res.kernel
                     assert (",false,cps=" if variant == "fast_nodet" else ",true,cps=") in res.kernel, res.kernel
-                    assert res.kernel.endswith("cps=1>" if variant == "fast_cps1" else "cps=2>"), res.kernel
+                    assert res.kernel.endswith("cps=2>" if variant == "fast_cps2" else "cps=1>"), res.kernel
             else:
                 assert "walk_philox<" in res.kernel                      # nt = 1: no step at all
             port = philox_port.walk_port(c1_csr, starts, counts, nt, 5, alias=tabs.alias_host, class_value=cv,

@@ -28,7 +28,7 @@ def main():
     starts = np.arange(csr.n_live)
     flush = torch.empty(512 << 20, dtype=torch.uint8, device=eng.device)
     knobs = ("NRW_CPS", "NRW_DET", "NRW_K1", "NRW_RANGE_TAIL", "NRW_TAIL_RANGES")
-    configs = [("default", {}), ("cps1", {"NRW_CPS": "1"}), ("single_range_size", {"NRW_TAIL_RANGES": "0"}),
+    configs = [("default", {}), ("cps2", {"NRW_CPS": "2"}), ("single_range_size", {"NRW_TAIL_RANGES": "0"}),
                ("always_draw", {"NRW_DET": "0"}), ("general", {"NRW_K1": "general"})]
     if len(sys.argv) > 3 and sys.argv[3] == "sweep":        # guided range sizes: smallest range x tail share
         configs = [("single_range_size", {"NRW_TAIL_RANGES": "0"}), ("general_control", {"NRW_K1": "general"})]
