@@ -27,7 +27,7 @@ def main():
     tabs = eng.upload(csr, node_class=nc)
     starts = np.arange(csr.n_live)
     flush = torch.empty(512 << 20, dtype=torch.uint8, device=eng.device)
-    knobs = ("NRW_CPS", "NRW_DET", "NRW_K1", "NRW_RANGE_TAIL", "NRW_TAIL_RANGES")
+    knobs = ("NRW_CPS", "NRW_DET", "NRW_K1", "NRW_RANGE_TAIL", "NRW_TAIL_RANGES", "NRW_RANGES_PER_WARP")
     configs = [("default", {}), ("cps2", {"NRW_CPS": "2"}), ("single_range_size", {"NRW_TAIL_RANGES": "0"}),
                ("always_draw", {"NRW_DET": "0"}), ("general", {"NRW_K1": "general"})]
     if len(sys.argv) > 3 and sys.argv[3] == "sweep":        # guided range sizes: smallest range x tail share
@@ -35,6 +35,10 @@ def main():
         for rt, tr in ((2048, 2), (1024, 2), (512, 2), (256, 2), (128, 2), (64, 2), (1024, 1), (1024, 3), (512, 1),
                        (512, 3), (1024, 4)):
             configs.append(("min%d_x%d" % (rt, tr), {"NRW_RANGE_TAIL": str(rt), "NRW_TAIL_RANGES": str(tr)}))
+        for rpw in (3, 4, 6, 12, 16, 24):
+            for rt, tr in ((1024, 2), (512, 2), (1024, 3)):
+                configs.append(("rpw%d_min%d_x%d" % (rpw, rt, tr), {"NRW_RANGES_PER_WARP": str(rpw), "NRW_RANGE_TAIL": str(rt),
+                                                                     "NRW_TAIL_RANGES": str(tr)}))
     for tag, env in configs:
         for k in knobs:
             os.environ.pop(k, None)
