@@ -391,12 +391,14 @@ def run_ours(args):
                     "frac": achieved / peak, "traffic": traffic, "kernel": res.kernel,
                     "kernel_ms": kernel_ms, "walker_steps_per_launch": steps_per_launch,
                     "algorithmic_bytes_per_walker_step": b_step, "peak_source": peak_src,
-                    "binding_resource": {"what": "SM integer math issue (ALU + FMA-heavy/IMAD pipes share the "
-                                                 "half-rate dispatch; their busy cycles add up to ~100 %), not memory",
+                    "binding_resource": {"what": "SM integer math issue (ALU and FMA-heavy/IMAD pipes at 57 % / 54 % of "
+                                                 "their half-rate peaks, issue slots 72 % busy, top stall = "
+                                                 "fixed-latency dependency), not memory",
                                          "issue_slot_utilisation_ncu": ncu_facts.get("issue_active_pct"),
                                          "alu_pipe_pct_ncu": ncu_facts.get("alu_pipe_pct"),
                                          "fmaheavy_pipe_pct_ncu": ncu_facts.get("fmaheavy_pipe_pct"),
                                          "warp_instructions_per_walker_step_ncu": ncu_facts.get("warp_inst_per_32_walker_steps"),
+                                         "smsp_active_share_of_elapsed_ncu": ncu_facts.get("smsp_active_share_of_elapsed"),
                                          "source": ncu_facts.get("source")},
                     "deterministic_step_fraction": det_frac,
                     "note": "algorithmic bytes are the reference algorithm's (SURVEY 8d: searchsorted "

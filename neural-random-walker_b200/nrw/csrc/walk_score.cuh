@@ -7,6 +7,9 @@
 //   * refill with ONE vote per iteration: dead lanes rank themselves with popc and take consecutive
 //     ids; everything rare (range exhausted, next start node, 2^32 carry of the stream id, walkers on
 //     absorbing starts) sits behind warp-uniform or [[unlikely]] branches;
+//   * id ranges of GUIDED size (fetch_range, walk_philox.cuh): big ranges first, the tail of the id space in
+//     phases of halving ranges, so that the warps finish together; a range that begins in another start
+//     node finds it by interpolation (locate_start) instead of bisection;
 //   * paired draws (common.cuh): a refill is followed by TWO steps sharing one Philox call -- lanes
 //     are only refilled at the top of the pair, so every live lane is at an even step;
 //   * the Philox round keys come from the kernel parameters (constant-bank operands), not from
