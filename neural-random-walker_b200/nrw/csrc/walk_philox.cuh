@@ -5,8 +5,9 @@
 //   * one thread per walker; a lane whose walker was absorbed / left through the sink is refilled
 //     at once from the warp's walker-id cursor (warp vote: __ballot_sync + popc ranks the dead
 //     lanes; no atomics), so lanes stay busy although the mean walk is only ~2 steps long;
-//   * warps pull contiguous walker-id ranges from one global counter (dynamic balance, one
-//     atomic per `range` walkers);
+//   * warps pull contiguous walker-id ranges from one global counter (dynamic balance); the range sizes
+//     are guided -- big first, halving over the tail of the id space (fetch_range below) -- so that the
+//     warps finish together;
 //   * Philox2x32-10 keyed by the seed with counter (walker id, step) -- (walker id, step pair) on
 //     compact tables, see common.cuh: any walker's trajectory is
 //     a pure function of (seed, id), independent of grid shape and of how ranks shard the ids;
@@ -84,8 +85,8 @@ __device__ __forceinline__ uint2 fac_row(const WalkParams& p, int k) {
                       leaves ? p.fac_exit_base : jn * (uint32_t)p.fac_period);
 }
 
-// Next id range [nb, nb + len) of a warp, or false when the launch's ids are exhausted (walk_score.cuh).
-// Ranges are numbered by TICKETS drawn from one global counter and their sizes are GUIDED: phase 0 hands
+// Next id range [nb, nb + len) of a warp, or false when the launch's ids are exhausted (walk_score.cuh and the
+// general kernel below).  Ranges are numbered by TICKETS drawn from one global counter and their sizes are GUIDED: phase 0 hands
 // out big ranges (few fetches), and the tail of the id space goes out in phases of ranges half as long
 // each, two ranges per warp and phase, down to `range_tail` ids -- so that the warps finish together.  With one range size the SM sub-partitions were
 // active for 88 % of the kernel on average: a warp that draws a heavy range last finishes up to one range
@@ -282,14 +283,11 @@ walk_philox_kernel(const __grid_constant__ WalkParams p) {
         if (need) {
             if (cur >= end) {
                 if (!exhausted) {
-                    long long a = 0;
-                    if (lane == 0) a = (long long)atomicAdd(p.work_next, (unsigned long long)p.range);
-                    a = __shfl_sync(NRW_FULL_MASK, a, 0);
-                    const long long nb = p.lo + a;
+                    long long nb = 0, len = 0;
                     cur = 0;
-                    if (nb >= p.hi) { exhausted = true; end = 0; }
+                    if (!fetch_range(p, lane, nb, len)) { exhausted = true; end = 0; }
                     else {
-                        end = (uint32_t)min(p.range, p.hi - nb);
+                        end = (uint32_t)len;
                         wwalk += end;
                         sid_base += nb - rbase;                  // same start, new range origin
                         rbase = nb;
@@ -312,12 +310,7 @@ walk_philox_kernel(const __grid_constant__ WalkParams p) {
                         if (gnew < e2) { ++s; s_end = e2; found = true; }
                     }
                     if (!found) {
-                        int lo_i = 0, hi_i = p.n_starts;
-                        while (hi_i - lo_i > 1) {
-                            const int mid = (lo_i + hi_i) >> 1;
-                            if (__ldg(p.start_prefix + mid) <= gnew) lo_i = mid; else hi_i = mid;
-                        }
-                        s = lo_i;
+                        s = locate_start(p, gnew);
                         s_lo = __ldg(p.start_prefix + s);
                         s_end = __ldg(p.start_prefix + s + 1);
                     }
