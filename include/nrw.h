@@ -248,6 +248,18 @@ NRW_API int  nrw_p2p_allreduce_i64(nrw_engine* e, int64_t* out, const void* peer
 NRW_API int  nrw_microbench(nrw_engine* e, int32_t kind, int32_t n, int32_t iters, const void* table,
                     unsigned long long* hist, unsigned long long* scratch, void* stream);
 
+/* The walk's work distribution, exposed for tests (no device needed): warps draw TICKETS from one counter
+ * and ticket t of phase j is the id range [start[j] + (t - ticket[j]) * range_of_phase[j], ... ) clipped at
+ * start[j+1].  Phase 0 hands out ranges of `range` ids; the last `tail_ranges` such ranges per warp of the
+ * n ids go out in phases of halving range length down to `range_tail`.  The phases tile [0, n) exactly
+ * once.  Arrays: start, ticket hold NRW_MAX_PHASES + 1 entries, range_of_phase NRW_MAX_PHASES.
+ * Replaces the reference's serial `for i in range(meshSize)` (fluence_mini_app.py:397) as the unit of
+ * work hand-out.                                                                                    */
+#define NRW_MAX_PHASES 8
+NRW_API int  nrw_guided_phases(int64_t n, int64_t range, int64_t warps, int64_t range_tail,
+                               int64_t tail_ranges, int64_t* start, int64_t* ticket,
+                               int64_t* range_of_phase, int32_t* n_phase);
+
 #ifdef __cplusplus
 }
 #endif

@@ -185,6 +185,48 @@ static int table_bytes(long long n, int elem) {
     return b > (1ll << 29) ? (1 << 29) : (int)b;
 }
 
+// Guided range sizes: phase 0 = ranges of `range` ids; the last `tail_ranges` big ranges per warp of the id
+// space go out in phases of ranges half as long each (two per warp and phase) down to `range_tail` ids (a
+// multiple of 32, >= 32).  Phase j covers ids [start[j], start[j+1]) with tickets ticket[j] .. ticket[j+1]-1;
+// the phases tile [0, n) exactly once.  Returns the number of phases (<= NRW_MAX_PHASES).
+static int guided_phases(long long n, long long range, long long warps, long long range_tail,
+                         long long tail_ranges, long long* start, long long* ticket, long long* rng) {
+    long long rt = (range_tail / 32) * 32;
+    if (rt < 32) rt = 32;
+    if (rt > range) rt = range;
+    long long tail_ids = tail_ranges <= 0 ? 0 : tail_ranges * range * warps;
+    if (tail_ids > n || tail_ids < 0) tail_ids = n;
+    int np = 0;
+    long long at = 0, tk = 0, r = range;
+    while (true) {
+        const bool last = np == NRW_MAX_PHASES - 1 || r <= rt || tail_ids == 0;
+        const long long stop = last ? n : n - tail_ids;         // this phase covers [at, stop)
+        if (stop > at || last) {
+            start[np] = at; ticket[np] = tk; rng[np] = r;
+            tk += (stop - at + r - 1) / r;
+            at = stop;
+            ++np;
+        }
+        if (last) break;
+        r = std::max(rt, ((r / 2) / 32) * 32);
+        tail_ids /= 2;
+    }
+    start[np] = n; ticket[np] = tk;
+    return np;
+}
+
+extern "C" int nrw_guided_phases(int64_t n, int64_t range, int64_t warps, int64_t range_tail, int64_t tail_ranges,
+                                 int64_t* start, int64_t* ticket, int64_t* range_of_phase, int32_t* n_phase) {
+    if (n < 0 || range < 1 || warps < 1 || !start || !ticket || !range_of_phase || !n_phase)
+        return fail(NRW_EINVAL, "nrw_guided_phases: bad argument");
+    long long st[NRW_MAX_PHASES + 1], tk[NRW_MAX_PHASES + 1], rg[NRW_MAX_PHASES];
+    const int np = guided_phases(n, range, warps, range_tail, tail_ranges, st, tk, rg);
+    for (int i = 0; i <= np; ++i) { start[i] = st[i]; ticket[i] = tk[i]; }
+    for (int i = 0; i < np; ++i) range_of_phase[i] = rg[i];
+    *n_phase = np;
+    return NRW_OK;
+}
+
 static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, WalkPlan* plan) {
     if (!e || !t || !w) return fail(NRW_EINVAL, "nrw_walk_philox: NULL argument");
     if (t->n_rows <= 0 || t->n_live < 0 || t->n_live > t->n_rows)
@@ -403,36 +445,13 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
 #undef Y
         }
     }
-    {   // guided range sizes (fetch_range, walk_philox.cuh): phase 0 = big ranges; the last `tail_ranges` big
-        // ranges per warp of the id space go out in phases of ranges half as long each (two per warp and
-        // phase) down to range_tail ids.  NRW_RANGE_TAIL / NRW_TAIL_RANGES override (0 ranges = one size)
+    {   // guided range sizes (fetch_range, walk_philox.cuh).  NRW_RANGE_TAIL / NRW_TAIL_RANGES override
+        // (0 ranges = one size)
         const char* rt_env = getenv("NRW_RANGE_TAIL");
         const char* tr_env = getenv("NRW_TAIL_RANGES");
-        long long rt = rt_env ? atoll(rt_env) : 1024;
-        rt = (rt / 32) * 32;
-        if (rt < 32) rt = 32;
-        if (rt > p.range) rt = p.range;
-        const long long tail_ranges = tr_env ? atoll(tr_env) : 2;
         const long long warps = (long long)plan->grid * (plan->block / 32);
-        long long tail_ids = tail_ranges <= 0 ? 0 : tail_ranges * p.range * warps;
-        if (tail_ids > n) tail_ids = n;
-        int np = 0;
-        long long start = 0, ticket = 0, r = p.range;
-        while (true) {
-            const bool last = np == NRW_MAX_PHASES - 1 || r <= rt || tail_ids == 0;
-            const long long stop = last ? n : n - tail_ids;         // this phase covers [start, stop)
-            if (stop > start || last) {
-                p.ph_start[np] = start; p.ph_ticket[np] = ticket; p.ph_range[np] = r;
-                ticket += (stop - start + r - 1) / r;
-                start = stop;
-                ++np;
-            }
-            if (last) break;
-            r = std::max(rt, ((r / 2) / 32) * 32);
-            tail_ids /= 2;
-        }
-        p.n_phase = np;
-        p.ph_start[np] = n; p.ph_ticket[np] = ticket;
+        p.n_phase = guided_phases(n, p.range, warps, rt_env ? atoll(rt_env) : 1024, tr_env ? atoll(tr_env) : 2,
+                                  p.ph_start, p.ph_ticket, p.ph_range);
     }
     if (!plan->fn)
         return fail(NRW_EINVAL, "nrw_walk_philox: tally combination %d is not built for table mode %d "

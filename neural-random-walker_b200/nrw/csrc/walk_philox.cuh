@@ -33,8 +33,7 @@ enum : int { TAB_SMEM = 0, TAB_HYB = 1, TAB_GLB = 2, TAB_CDF = 3, TAB_FAC = 4 };
 __host__ __device__ constexpr bool tab_compact(int tab) { return tab == TAB_SMEM || tab == TAB_HYB || tab == TAB_FAC; }
 enum : int { TL_SCORE = 1, TL_TW = 2, TL_HIST_S = 4, TL_HIST_G = 8, TL_CNT_S = 16, TL_CNT_G = 32 };
 
-constexpr int WALK_THREADS = 1024;
-constexpr int NRW_MAX_PHASES = 8;
+constexpr int WALK_THREADS = 1024;   // NRW_MAX_PHASES (guided range sizes): include/nrw.h
 
 struct WalkParams {
     int n_rows, n_live, n_alias;

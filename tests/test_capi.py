@@ -67,3 +67,46 @@ def test_create_without_gpu_fails_with_a_message():
     assert lib.nrw_walk_philox(None, None, None, None) == -1
     assert lib.nrw_walk_replay(None, None, None, None) == -1
     assert lib.nrw_device_info(None, None, None) == -1
+
+
+def _phases(lib, n, rng, warps, range_tail, tail_ranges):
+    import numpy as np
+    start = np.zeros(9, np.int64); ticket = np.zeros(9, np.int64); r = np.zeros(8, np.int64)
+    k = C.c_int32()
+    rc = lib.nrw_guided_phases(n, rng, warps, range_tail, tail_ranges, start.ctypes.data, ticket.ctypes.data,
+                               r.ctypes.data, C.byref(k))
+    assert rc == 0, lib.nrw_last_error()
+    return start[:k.value + 1], ticket[:k.value + 1], r[:k.value]
+
+
+def test_guided_range_phases_tile_the_id_space():
+    """The walk hands out its walker ids as tickets -> ranges of guided size (walk_philox.cuh::fetch_range,
+    planner nrw_guided_phases): every id must belong to exactly one ticket, whatever the sizes."""
+    import numpy as np
+    from hypothesis import given, settings, strategies as st
+    from nrw import engine
+    lib = engine.load_library()
+
+    # the bench launch: 1.25e8 ids, 148 x 32 warps, big ranges of 4096 ids (six per warp, capped), tail down to 1024
+    start, ticket, r = _phases(lib, 125_000_000, 4096, 4736, 1024, 2)
+    assert list(r) == [4096, 2048, 1024] and start[0] == 0 and start[-1] == 125_000_000
+    assert start[1] == 125_000_000 - 2 * 4096 * 4736                     # the tail: two big ranges per warp
+    assert ticket[-1] < 12 * 4736                                        # ~10 tickets per warp
+
+    @settings(max_examples=300, deadline=None)
+    @given(n=st.integers(0, 200_000), rng=st.integers(1, 5000), warps=st.integers(1, 64),
+           rt=st.integers(0, 6000), tr=st.integers(-1, 5))
+    def check(n, rng, warps, rt, tr):
+        start, ticket, r = _phases(lib, n, rng, warps, rt, tr)
+        k = len(r)
+        assert 1 <= k <= 8 and start[0] == 0 and start[-1] == n and ticket[0] == 0
+        assert (np.diff(start) >= 0).all() and (np.diff(r) <= 0).all() and (r >= 1).all()
+        covered = np.zeros(n, np.int32)
+        for t in range(int(ticket[-1])):                                 # fetch_range's mapping
+            j = int(np.searchsorted(ticket, t, side="right") - 1)
+            a = start[j] + (t - ticket[j]) * r[j]
+            assert a < start[j + 1]
+            covered[a:min(a + r[j], start[j + 1])] += 1
+        assert (covered == 1).all()
+    check()
+    assert lib.nrw_guided_phases(-1, 32, 1, 32, 2, None, None, None, None) == -1
