@@ -15,7 +15,17 @@
  *     hundred bytes of per-handle scratch; functions whose name ends in _host take HOST
  *     pointers and do their own staging;
  *   - `stream` is a cudaStream_t passed as void*; NULL means the legacy default stream;
- *   - nothing here synchronises unless the comment says so.
+ *   - nothing here synchronises unless the comment says so;
+ *   - threading: an engine may be used from several host threads and several streams at once.  Every
+ *     walk launch takes its own ticket slot (work hand-out counter) from a ring of NRW_TICKET_SLOTS
+ *     slots that the launch itself hands back when its last block retires, so launches of one engine
+ *     that overlap on different streams do not share any device state (at most NRW_TICKET_SLOTS may
+ *     be in flight at once).  The *_host entries stage through per-engine buffers and serialise
+ *     behind a per-engine mutex;
+ *   - environment: the measurement switches (NRW_K1, NRW_DET, NRW_TAB, NRW_CPS, NRW_RANGES_PER_WARP,
+ *     NRW_RANGE_TAIL, NRW_TAIL_RANGES, NRW_CNT_MATCH, NRW_CNT_CACHE, NRW_CNT_PATH)
+ *     are read ONCE, in nrw_create, and stored in the handle (nrw_engine_config prints them); no
+ *     launch calls getenv.  None of them changes a result.
  */
 #ifndef NRW_H_
 #define NRW_H_
@@ -26,7 +36,7 @@
 extern "C" {
 #endif
 
-#define NRW_ABI_VERSION 2
+#define NRW_ABI_VERSION 3
 
 #if defined(__GNUC__)
 #define NRW_API __attribute__((visibility("default")))
@@ -40,6 +50,7 @@ extern "C" {
 #define NRW_ENOSPC       -3   /* shared memory / buffer capacity exceeded           */
 
 typedef struct nrw_engine nrw_engine;   /* opaque handle: one per (process, device) */
+#define NRW_TICKET_SLOTS 1024
 
 /* ---- table layouts -------------------------------------------------------------- */
 /* alias_layout values */
@@ -88,12 +99,23 @@ typedef struct nrw_tables {
     int32_t  fac_period, fac_cells, fac_n_tail;
     int32_t  fac_shift;       /* k / fac_period == (k * fac_magic) >> fac_shift, k < n_live */
     uint32_t fac_magic, fac_exit_w0, fac_exit_base;
+    /* Optional (NRW_SAMPLER_TREE): the probability circuit of loihirw/rw_core.py:11-156 as a device table.
+     * Row r's successors (its CSR entries, padded with impossible outputs to n2 = the next power of two) are the
+     * leaves of a complete binary tree; tree[tree_ptr[r] + h] is the firing threshold of the probability neuron
+     * at heap index h (root 0, children 2h+1 / 2h+2): floor(128 * p_left), i.e. the 8-bit synaptic weight
+     * 128*p+36 of rw_core.py:151-153 with its offset removed.  A draw walks log2(n2) levels, one 7-bit
+     * uniform per level: left iff u7 < threshold.  NULL when absent.                                    */
+    const uint8_t* tree;      /* [tree_ptr[n_rows]]                                        */
+    const int32_t* tree_ptr;  /* [n_rows + 1]; row r owns n2(r) - 1 entries (0 for n <= 1) */
 } nrw_tables;
 
 /* ---- Philox walk (K1) -------------------------------------------------------------- */
 #define NRW_SAMPLER_ALIAS 0   /* O(1) alias draw (WIDE: slot = mulhi(r0, n), coin = r1)   */
 #define NRW_SAMPLER_CDF   1   /* the reference's searchsorted(left) on the fp64 prefix
                                  sums with u = ((r0>>5)*2^26 + (r1>>6)) / 2^53            */
+#define NRW_SAMPLER_TREE  2   /* Loihi-faithful: walk the row's binary tree of 8-bit Bernoulli
+                                 weights (nrw_tables.tree; rows of <= 512 entries); one Philox
+                                 call per step, level l uses bits [7l, 7l+7) of (r0 | r1 << 32) */
 
 #define NRW_COUNTER_STEPS     0   /* walker-steps == uniform draws (fluence_mini_app.py:243)   */
 #define NRW_COUNTER_EXITS     1   /* arrivals on absorbing rows                                */
@@ -101,6 +123,31 @@ typedef struct nrw_tables {
 #define NRW_COUNTER_TOVERFLOW 3   /* tallies dropped because t >= t_cap (count_tn only)        */
 #define NRW_COUNTER_WALKERS   4   /* walkers started                                           */
 #define NRW_N_COUNTERS        8
+
+/* ---- the path's one collective, fused into the walk (N > 1), and the zeroing of the next tally buffer ---
+ * The per-start scores and the counters of a launch live in ONE int64 buffer per rank,
+ * own_buf[offset, offset + n) (nrw_walk.score and nrw_walk.counters must point into it).  When the last
+ * block of the launch retires it (world > 1) publishes `epoch` to every peer, waits for theirs, sums all
+ * ranks' vectors over NVLink peer memory into out[0, n) and writes out[n] = 0 (1 if a peer did not arrive
+ * within 5 s: the sums are then invalid and no buffer was zeroed -- test it per solve); then it zeroes
+ * own_buf[zero_offset, zero_offset + n) (zero_offset < 0: nothing).  Callers alternate two halves of
+ * own_buf by epoch parity (offset = (epoch & 1) * n', zero_offset = the other half): a half is zeroed only
+ * after the wait of the following epoch, which proves that every peer has finished reading it, so one
+ * signal / wait per solve suffices and no memset is ever launched.  world == 1: no exchange, `out` may be
+ * NULL; the tail only zeroes the next half.  peer_bufs_dev / peer_flags_dev: DEVICE arrays of `world`
+ * pointers -- every rank's buffer (int64) and flag array (uint64[world], zero-initialised) as mapped
+ * into this process (symmetric memory / CUDA IPC; nrw/dist.py uses torch's symmetric-memory allocator);
+ * `epoch` > 0 and increases by one per launch on every rank.  Replaces the all-reduce a multi-process
+ * run(args) of fluence_mini_app.py:397-438 needs once per solve.                                      */
+typedef struct nrw_reduce {
+    int32_t  rank, world;
+    const void* peer_bufs_dev;      /* NULL when world == 1                              */
+    const void* peer_flags_dev;     /* NULL when world == 1                              */
+    int64_t* own_buf;
+    int64_t  offset, zero_offset, n;
+    uint64_t epoch;
+    int64_t* out;                   /* [n + 1] (device)                                  */
+} nrw_reduce;
 
 typedef struct nrw_walk {
     /* walkers: global walker id g in [0, start_prefix[n_starts]); walker g starts on
@@ -115,7 +162,9 @@ typedef struct nrw_walk {
      * when start_id_base is NULL.  Lets a rank walk a slice of EVERY start's walkers while
      * each walker keeps the stream it has in the unsharded run.  ids must be < 2^40.    */
     const int64_t* start_id_base;   /* [n_starts] or NULL                                */
-    uint64_t seed;                  /* Philox key = hash(seed); counter = (stream id, step), or (stream id, step pair) on COMPACT tables: csrc/common.cuh */
+    uint64_t seed;                  /* Philox key = 32-bit hash of the seed (splitmix64 finaliser folded to 32 bits, csrc/common.cuh
+                                       seed_to_key): 2^32 distinct stream families; counter = (stream id, step), or
+                                       (stream id, step pair) on COMPACT tables */
     int32_t  nt;                    /* neuraltime: model steps t = 1 .. nt-1 (:236)      */
     int32_t  sampler;               /* NRW_SAMPLER_*                                     */
 
@@ -146,6 +195,16 @@ typedef struct nrw_walk {
     int32_t  count_per_start;
 
     unsigned long long* counters;   /* [NRW_N_COUNTERS], accumulated (caller zeroes)     */
+
+    /* optional: the most likely trajectory of every start, count_path[s * t_cap + t] = node at step t
+     * (t = 0: the start node) following each row's most probable successor.  With count_tn in global
+     * memory, a walker that is still on its start's path is not tallied step by step: a per-block
+     * shared-memory histogram of the steps at which walkers LEAVE the path gives the path bins exactly
+     * (count on the path at t = walkers that left later), one shared-memory atomic per walker
+     * instead of one contended global atomic per step.  Same counts, bit for bit.  NULL: off.     */
+    const int32_t* count_path;
+
+    const nrw_reduce* reduce;       /* HOST pointer, read at launch; NULL: no tail work  */
 } nrw_walk;
 
 /* ---- replay walk (K2): bit-exact with the reference under its own uniform stream ----- */
@@ -172,7 +231,10 @@ typedef struct nrw_replay {
 NRW_API int  nrw_abi_version(void);
 NRW_API const char* nrw_last_error(void);
 
+/* reads the NRW_* measurement switches from the environment (once) */
 NRW_API int  nrw_create(int device, nrw_engine** out);
+/* the switches as resolved at nrw_create, "name=value ..." (for logs and bench lines) */
+NRW_API int  nrw_engine_config(nrw_engine* e, char* buf, int buf_len);
 NRW_API int  nrw_destroy(nrw_engine* e);
 /* number of SMs, max opt-in shared memory per block, of the engine's device */
 NRW_API int  nrw_device_info(nrw_engine* e, int* n_sms, int* max_smem_bytes);
@@ -213,16 +275,19 @@ NRW_API int  nrw_expand_counts(nrw_engine* e, const uint32_t* count_tn, int32_t 
 
 /* End-to-end convenience with HOST buffers (what `bench.py` times as e2e): copies the
  * compact alias tables and the start list to the device, runs K1 in score mode, copies
- * score / counters back and synchronises `stream`.                                        */
+ * score / counters back and synchronises `stream`.  `reduce` NULL: single GPU, the engine's own
+ * tally buffer.  With `reduce` (N > 1; n must be n_starts + NRW_N_COUNTERS): the walk tallies into
+ * reduce->own_buf + offset, the sums over ranks come back from reduce->out, and the call fails with
+ * NRW_ECUDA if a peer timed out.  start_id_base_host may be NULL.                          */
 NRW_API int  nrw_fluence_scores_host(nrw_engine* e,
                              int32_t n_rows, int32_t n_live, int32_t n_alias,
                              const void* rowinfo_host, const void* alias_host,
                              int32_t n_starts, const int32_t* start_nodes_host,
-                             const int64_t* start_prefix_host,
+                             const int64_t* start_prefix_host, const int64_t* start_id_base_host,
                              int64_t walker_lo, int64_t walker_hi, uint64_t seed, int32_t nt,
                              const double class_value[4],
                              int64_t* score_host, unsigned long long* counters_host,
-                             void* stream);
+                             const nrw_reduce* reduce, void* stream);
 
 /* The path's one collective over peer memory (no NCCL): out[i] = sum over ranks q of
  * peer_bufs[q][offset + i].  peer_bufs_dev / peer_flags_dev are DEVICE arrays of `world` pointers:
@@ -232,7 +297,8 @@ NRW_API int  nrw_fluence_scores_host(nrw_engine* e,
  * for theirs, then reads and sums.  Alternate `offset` between two buffers per epoch: a buffer may be
  * rewritten once the NEXT call has been enqueued; zero_offset >= 0 makes the kernel zero this rank's
  * own buffer at that offset after the wait (the buffer of the next step), -1 leaves it.  *err_flag (device int) is set to 1 if a peer does
- * not arrive within 5 s.  Replaces the all-reduce a multi-process run(args) of
+ * not arrive within 5 s (%globaltimer); `out` and the buffers are then left untouched.  The walk runs the same exchange in its own tail
+ * (nrw_walk.reduce); this entry serves tallies no single walk launch produced.  Replaces the all-reduce a multi-process run(args) of
  * fluence_mini_app.py:397-438 needs once per solve. */
 NRW_API int  nrw_p2p_allreduce_i64(nrw_engine* e, int64_t* out, const void* peer_bufs_dev,
                                    const void* peer_flags_dev, int64_t offset, int64_t zero_offset,

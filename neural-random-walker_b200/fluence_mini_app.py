@@ -83,9 +83,12 @@ def run(args):
     source = mesh.SOURCES[args.get('source', 'default')] if args.get('source', 'default') != 'default' \
         else sourceTerm
 
+    global last_run_split
+    split = {}
+    t_run = time.perf_counter()
     rank, world = ndist.init_from_env()        # under torchrun: one process per GPU, rank 0 writes the files
     try:
-        csr = mesh.build_fluence_csr(dt, da, v, SigS, L)              # :279-381
+        csr = mesh.build_fluence_csr_cached(dt, da, v, SigS, L)       # :279-381 (memoised by the parameters)
     except ValueError:
         rw_logger.error("The probability of more than one scattering event occurring in a single "
                         "time step is greater than 0.05.")
@@ -95,15 +98,19 @@ def run(args):
     m = csr.meta['mesh']
     meshSize, NS, ND = m['meshSize'], m['NS'], m['ND']
     rw_logger.info('Mesh Size: {}'.format(meshSize))
+    split['csr_build_s'] = time.perf_counter() - t_run
     if csr.n_rows > mesh.MAX_DENSE_CSV_ROWS:
         matrix_filename = os.path.splitext(matrix_filename)[0] + '.npz'
+        rw_logger.warning("matrix has {} rows: saved as CSR in {} instead of a dense CSV".format(
+            csr.n_rows, matrix_filename))
+    writer = None
     if rank == 0 or rmode != 'pc':
-        if csr.n_rows <= mesh.MAX_DENSE_CSV_ROWS:
-            mesh.save_matrix_csv(matrix_filename, csr)                # :384, byte-identical text
-        else:
-            mesh.save_matrix_npz(matrix_filename, csr)
-            rw_logger.warning("matrix has {} rows: saved as CSR in {} instead of a dense CSV".format(
-                csr.n_rows, matrix_filename))
+        # :384 (byte-identical text for meshes a dense CSV can hold).  The fused pc path walks the in-memory CSR,
+        # so the file is written in the background while the GPU works; every other back end reads it by name
+        # and waits for it here
+        writer = mesh.MatrixFileWriter(matrix_filename, csr)
+        if not (rmode == 'pc' and run_functions['pc'] is run_pc):
+            writer.join()
     rw_logger.info("Transition matrix construction complete")
     rw_logger.info("    matrix saved to {}".format(matrix_filename))
 
@@ -116,6 +123,13 @@ def run(args):
                             sampler=args.get('sampler', 'alias'))
         rwSol = res.rwSol
         el = time.time() - t0
+        split['solve_s'] = el
+        split['walker_steps'] = int(res.walker_steps)
+        split['rng'] = res.rng
+        split.update(res.split)
+        if res.rng == 'replay' and args.get('rng', 'auto') in (None, 'auto'):
+            rw_logger.info("    --rng auto chose the bit-exact replay of numpy's stream (one CTA, sequential over start "
+                           "nodes, ~2e6 walker-steps/s); --rng philox walks the same mesh at > 1e11 walker-steps/s")
         rw_logger.info('    {} mesh points, {} walker-steps, rng={} in {:.4f} s ({:.3e} walker-steps/s)'
                        .format(meshSize, res.walker_steps, res.rng, el, res.walker_steps / max(el, 1e-12)))
     else:
@@ -147,9 +161,22 @@ def run(args):
     if rank == 0:
         if args['plot_results']:
             plot_results(rwSol, m['dirs'], m['space'], results_filename)
+        t0 = time.perf_counter()
         np.savetxt(results_filename, rwSol, delimiter=",")            # :446
+        split['results_file_s'] = time.perf_counter() - t0
         rw_logger.info("Solution saved to {}".format(results_filename))
+    if writer is not None:
+        t0 = time.perf_counter()
+        writer.join()                                                 # the matrix file is complete on return
+        split['matrix_file_wait_s'] = time.perf_counter() - t0
+        split['matrix_file_skipped_unchanged'] = writer.skipped
+    split['total_s'] = time.perf_counter() - t_run
+    last_run_split = split
+    rw_logger.debug("run() split: {}".format(split))
     return rwSol
+
+
+last_run_split = {}       # where the time of the most recent run(args) went (seconds; bench.py e2e_run_args)
 
 
 def plot_results(data, angles, spaces, rfilename):

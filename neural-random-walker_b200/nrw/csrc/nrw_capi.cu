@@ -5,7 +5,10 @@
 #include <cstdarg>
 #include <cstdio>
 #include <algorithm>
+#include <atomic>
 #include <cstring>
+#include <mutex>
+#include <unordered_map>
 
 #include "common.cuh"
 #include "microbench.cuh"
@@ -36,20 +39,59 @@ static int fail(int code, const char* fmt, ...) {
                         __FILE__, __LINE__);                                                  \
     } while (0)
 
+// The measurement switches, read from the environment ONCE in nrw_create.
+struct nrw_config {
+    int k1_general;        // NRW_K1=general: score walks take the general kernel
+    int det;               // NRW_DET=0: draw on rows with a single absorbing successor too
+    int tab;               // NRW_TAB: 0 auto, 1 hyb (descriptors L2-resident), 2 fac (factored descriptors)
+    int cps;               // NRW_CPS=2: two CTAs of 768 threads per SM when the tables leave room
+    long long ranges_per_warp, range_tail, tail_ranges;
+    int cnt_match;         // NRW_CNT_MATCH: -1 auto, 0 plain, 1 match_any aggregation
+    int cnt_cache;         // NRW_CNT_CACHE=0: no CTA-level cache of hot bins
+    int cnt_path;          // NRW_CNT_PATH=0: ignore nrw_walk.count_path
+};
+
 struct nrw_engine {
     int device;
     int n_sms;
     int max_smem;
-    int clock_khz;                   // SM clock (cached: the attribute query costs ~1 ms per call)
-    unsigned long long* work_next;   // device counter the warps pull walker-id ranges from
+    nrw_config cfg;
+    // ring of ticket slots {work_next, done}: one per launch, handed back by the launch's last CTA (walk_tail.cuh)
+    unsigned long long* slots;
+    std::atomic<unsigned long long> next_slot;
+    std::mutex mu;                                            // attribute cache
+    std::mutex mu_host;                                       // the *_host staging buffers (calls serialise)
+    std::unordered_map<const void*, int> smem_attr;           // kernel -> dynamic shared memory already opted in
     // grow-only staging buffers of nrw_fluence_scores_host
     void* d_rowinfo; size_t cap_rowinfo;
     void* d_alias; size_t cap_alias;
     void* d_starts; size_t cap_starts;
     void* d_prefix; size_t cap_prefix;
-    void* d_score; size_t cap_score;
-    unsigned long long* d_counters;
+    void* d_idbase; size_t cap_idbase;
+    void* d_tally; size_t cap_tally;                          // scores, then NRW_N_COUNTERS counters
 };
+
+static int env_int(const char* name, int dflt) {
+    const char* v = getenv(name);
+    return v && *v ? atoi(v) : dflt;
+}
+static nrw_config config_from_env() {
+    nrw_config c;
+    const char* k1 = getenv("NRW_K1");
+    c.k1_general = k1 && strcmp(k1, "general") == 0;
+    c.det = env_int("NRW_DET", 1) != 0;
+    const char* tab = getenv("NRW_TAB");
+    c.tab = tab && strcmp(tab, "hyb") == 0 ? 1 : (tab && strcmp(tab, "fac") == 0 ? 2 : 0);
+    c.cps = env_int("NRW_CPS", 1) == 2 ? 2 : 1;
+    c.ranges_per_warp = env_int("NRW_RANGES_PER_WARP", 6);
+    if (c.ranges_per_warp < 1) c.ranges_per_warp = 6;
+    c.range_tail = env_int("NRW_RANGE_TAIL", 1024);
+    c.tail_ranges = env_int("NRW_TAIL_RANGES", 2);
+    c.cnt_match = getenv("NRW_CNT_MATCH") ? (env_int("NRW_CNT_MATCH", 1) != 0) : -1;
+    c.cnt_cache = env_int("NRW_CNT_CACHE", 1) != 0;
+    c.cnt_path = env_int("NRW_CNT_PATH", 1) != 0;
+    return c;
+}
 
 extern "C" int nrw_abi_version(void) { return NRW_ABI_VERSION; }
 extern "C" const char* nrw_last_error(void) { return g_err; }
@@ -67,13 +109,17 @@ extern "C" int nrw_create(int device, nrw_engine** out) {
         return fail(NRW_EINVAL, "nrw_create: device %d is sm_%d%d; libnrw is built for sm_100a only",
                     device, prop.major, prop.minor);
     nrw_engine* e = new nrw_engine();
-    memset(e, 0, sizeof(*e));
     e->device = device;
     e->n_sms = prop.multiProcessorCount;
     e->max_smem = (int)prop.sharedMemPerBlockOptin;
-    e->clock_khz = prop.clockRate > 0 ? prop.clockRate : 2000000;
-    cudaError_t err = cudaMalloc(&e->work_next, sizeof(unsigned long long));
-    if (err == cudaSuccess) err = cudaMalloc(&e->d_counters, NRW_N_COUNTERS * sizeof(unsigned long long));
+    e->cfg = config_from_env();
+    e->slots = nullptr;
+    e->next_slot = 0;
+    e->d_rowinfo = e->d_alias = e->d_starts = e->d_prefix = e->d_idbase = e->d_tally = nullptr;
+    e->cap_rowinfo = e->cap_alias = e->cap_starts = e->cap_prefix = e->cap_idbase = e->cap_tally = 0;
+    const size_t slot_bytes = (size_t)NRW_TICKET_SLOTS * 2 * sizeof(unsigned long long);
+    cudaError_t err = cudaMalloc(&e->slots, slot_bytes);
+    if (err == cudaSuccess) err = cudaMemset(e->slots, 0, slot_bytes);
     if (err != cudaSuccess) {
         nrw_destroy(e);                                   // frees whatever was allocated
         return fail(NRW_ECUDA, "nrw_create: cudaMalloc failed: %s", cudaGetErrorString(err));
@@ -85,11 +131,21 @@ extern "C" int nrw_create(int device, nrw_engine** out) {
 extern "C" int nrw_destroy(nrw_engine* e) {
     if (!e) return NRW_OK;
     cudaSetDevice(e->device);
-    cudaFree(e->work_next);
-    cudaFree(e->d_counters);
+    cudaFree(e->slots);
     cudaFree(e->d_rowinfo); cudaFree(e->d_alias); cudaFree(e->d_starts);
-    cudaFree(e->d_prefix); cudaFree(e->d_score);
+    cudaFree(e->d_prefix); cudaFree(e->d_idbase); cudaFree(e->d_tally);
     delete e;
+    return NRW_OK;
+}
+
+extern "C" int nrw_engine_config(nrw_engine* e, char* buf, int buf_len) {
+    if (!e || !buf || buf_len <= 0) return fail(NRW_EINVAL, "nrw_engine_config: bad argument");
+    const nrw_config& c = e->cfg;
+    snprintf(buf, (size_t)buf_len,
+             "k1=%s det=%d tab=%s cps=%d ranges_per_warp=%lld range_tail=%lld tail_ranges=%lld cnt_match=%d "
+             "cnt_cache=%d cnt_path=%d", c.k1_general ? "general" : "auto", c.det,
+             c.tab == 1 ? "hyb" : (c.tab == 2 ? "fac" : "auto"), c.cps, c.ranges_per_warp, c.range_tail,
+             c.tail_ranges, c.cnt_match, c.cnt_cache, c.cnt_path);
     return NRW_OK;
 }
 
@@ -176,7 +232,8 @@ struct WalkPlan {
     X(TAB_FAC, 1) X(TAB_FAC, 3) X(TAB_FAC, 4) X(TAB_FAC, 5) X(TAB_FAC, 8) X(TAB_FAC, 9)        \
     X(TAB_FAC, 32)                                                                             \
     X(TAB_GLB, 1) X(TAB_GLB, 3) X(TAB_GLB, 8) X(TAB_GLB, 9) X(TAB_GLB, 16) X(TAB_GLB, 32)      \
-    X(TAB_CDF, 1) X(TAB_CDF, 3) X(TAB_CDF, 8) X(TAB_CDF, 9) X(TAB_CDF, 16) X(TAB_CDF, 32)
+    X(TAB_CDF, 1) X(TAB_CDF, 3) X(TAB_CDF, 8) X(TAB_CDF, 9) X(TAB_CDF, 16) X(TAB_CDF, 32)     \
+    X(TAB_TREE, 1) X(TAB_TREE, 3) X(TAB_TREE, 8) X(TAB_TREE, 9) X(TAB_TREE, 16) X(TAB_TREE, 32)
 
 static int align16(int x) { return (x + 15) & ~15; }
 // table sizes in bytes, clamped so that tables far beyond any shared memory cannot wrap an int
@@ -248,6 +305,7 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
     p.n_rows = t->n_rows; p.n_live = t->n_live; p.n_alias = t->n_alias;
     p.indptr = t->indptr; p.cols = t->cols; p.cum = t->cum; p.node_class = t->node_class;
     p.rowinfo = t->rowinfo; p.alias = t->alias;
+    p.tree = t->tree; p.tree_ptr = t->tree_ptr;
     p.n_starts = w->n_starts; p.start_nodes = w->start_nodes;
     p.start_prefix = (const long long*)w->start_prefix;
     p.start_id_base = (const long long*)w->start_id_base;
@@ -269,12 +327,33 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
     }
     p.node_hist = w->node_hist; p.count_tn = w->count_tn;
     p.t_cap = w->t_cap; p.per_start = w->count_per_start;
-    {   // warp-aggregated (match_any) or plain shared-memory atomics for the time-resolved counts:
-        // aggregation pays when walks are short and lanes share bins; NRW_CNT_MATCH=0/1 overrides
-        const char* m_env = getenv("NRW_CNT_MATCH");
-        p.cnt_match = m_env ? (strcmp(m_env, "0") != 0) : (w->t_cap <= 256);
+    // warp-aggregated (match_any) or plain shared-memory atomics for the time-resolved counts:
+    // aggregation pays when walks are short and lanes share bins; NRW_CNT_MATCH=0/1 overrides
+    p.cnt_match = e->cfg.cnt_match >= 0 ? e->cfg.cnt_match : (w->t_cap <= 256);
+    p.counters = w->counters; p.work_next = nullptr;          // the ticket slot is assigned at launch
+    p.tail.zero_off = -1; p.tail.world = 1;
+    p.tail.timeout_ns = 5000000000ull;                        // 5 s without a peer: give up (status word)
+    if (const nrw_reduce* r = w->reduce) {
+        if (r->world < 1 || r->world > 64 || r->rank < 0 || r->rank >= r->world || r->n <= 0 || r->offset < 0 ||
+            !r->own_buf || r->epoch == 0)
+            return fail(NRW_EINVAL, "nrw_walk_philox: bad reduce descriptor");
+        if (r->world > 1 && (!r->peer_bufs_dev || !r->peer_flags_dev || !r->out))
+            return fail(NRW_EINVAL, "nrw_walk_philox: reduce over %d ranks needs peer buffers, flags and out", r->world);
+        const long long* lo = (const long long*)r->own_buf + r->offset;
+        const long long* hi = lo + r->n;
+        if (w->score && ((const long long*)w->score < lo || (const long long*)w->score + w->n_starts > hi))
+            return fail(NRW_EINVAL, "nrw_walk_philox: score is not inside the reduce buffer");
+        if (w->counters && ((const long long*)w->counters < lo || (const long long*)w->counters + NRW_N_COUNTERS > hi))
+            return fail(NRW_EINVAL, "nrw_walk_philox: counters are not inside the reduce buffer");
+        p.tail.world = r->world; p.tail.rank = r->rank;
+        p.tail.bufs = (const long long* const*)r->peer_bufs_dev;
+        p.tail.flags = (unsigned long long* const*)r->peer_flags_dev;
+        p.tail.own = (long long*)r->own_buf;
+        p.tail.off = r->offset; p.tail.zero_off = r->zero_offset; p.tail.n = r->n;
+        p.tail.epoch = r->epoch;
+        p.tail.out = (long long*)r->out;
+        p.tail.status = r->out ? (long long*)r->out + r->n : nullptr;
     }
-    p.counters = w->counters; p.work_next = e->work_next;
     if (w->count_tn && w->t_cap < 1) return fail(NRW_EINVAL, "nrw_walk_philox: t_cap=%d", w->t_cap);
     if (w->count_tn && w->walker_hi - w->walker_lo >= (1ll << 32))
         return fail(NRW_EINVAL, "nrw_walk_philox: count_tn bins are 32-bit; walk fewer than 2^32 ids per launch");
@@ -285,6 +364,10 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
         if (!t->indptr || !t->cols || !t->cum)
             return fail(NRW_EINVAL, "nrw_walk_philox: cdf sampler needs indptr/cols/cum");
         tab = TAB_CDF;
+    } else if (w->sampler == NRW_SAMPLER_TREE) {
+        if (!t->indptr || !t->cols || !t->tree || !t->tree_ptr)
+            return fail(NRW_EINVAL, "nrw_walk_philox: tree sampler needs indptr/cols/tree/tree_ptr");
+        tab = TAB_TREE;
     } else if (w->sampler == NRW_SAMPLER_ALIAS) {
         if (!t->rowinfo || !t->alias || t->n_alias <= 0)
             return fail(NRW_EINVAL, "nrw_walk_philox: alias sampler needs rowinfo/alias tables");
@@ -302,8 +385,7 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
             const long long fbl = have_fac ? (long long)table_bytes(t->fac_period, 8) + table_bytes(t->fac_n_tail, 8) +
                                              table_bytes((t->n_live + 15) / 16, 4) : 0;
             const int fb = fbl > (1ll << 29) ? (1 << 29) : (int)fbl;
-            const char* tab_env = getenv("NRW_TAB");
-            const bool force_fac = tab_env && strcmp(tab_env, "fac") == 0, no_fac = tab_env && strcmp(tab_env, "hyb") == 0;
+            const bool force_fac = e->cfg.tab == 2, no_fac = e->cfg.tab == 1;
             if (force_fac && !(have_fac && 16 + ab + fb <= e->max_smem))
                 return fail(NRW_EINVAL, "nrw_walk_philox: NRW_TAB=fac but the tables carry no factored rows that fit");
             if (force_fac) tab = TAB_FAC;
@@ -350,11 +432,18 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
             tl |= TL_CNT_S; p.sm_cnt = smem; smem += align16((int)bins * 4); p.cnt_bins = (int)bins;
         } else {
             tl |= TL_CNT_G;
-            // spare shared memory becomes a cache of hot bins (walk_philox.cuh); a slot's 32-bit count
-            // cannot wrap while the launch has fewer than 2^32 walker-steps per bin: bound by walkers
-            const char* c_env = getenv("NRW_CNT_CACHE");             // NRW_CNT_CACHE=0 turns it off
+            // the likely path of every start, when the caller supplies it and its two small tables fit shared memory
+            // (NRW_CNT_PATH=0 ignores it): walkers on the path are tallied through a leave-time histogram
             const long long n_walkers = w->walker_hi - w->walker_lo;
-            if (!(c_env && strcmp(c_env, "0") == 0) && n_walkers < (1ll << 32)) {
+            const long long path_cells = (long long)w->n_starts * w->t_cap;
+            const long long path_bytes = (path_cells * 4 + 15) / 16 * 16, left_bytes = ((path_cells + w->n_starts) * 4 + 15) / 16 * 16;
+            if (w->count_path && e->cfg.cnt_path && n_walkers < (1ll << 32) && smem + path_bytes + left_bytes <= e->max_smem) {
+                p.cnt_path = w->count_path;
+                p.sm_path = smem; smem += (int)path_bytes;
+                p.sm_left = smem; smem += (int)left_bytes;
+            } else if (e->cfg.cnt_cache && n_walkers < (1ll << 32)) {
+                // spare shared memory becomes a cache of hot bins (walk_philox.cuh); a slot's 32-bit count
+                // cannot wrap while the launch has fewer than 2^32 walker-steps per bin: bound by walkers (NRW_CNT_CACHE=0 turns it off)
                 int bits = 14;                                        // 16384 slots x 8 B = 128 KB at most
                 while (bits >= 10 && smem + (8 << bits) > e->max_smem) --bits;
                 if (bits >= 10) { p.sm_ccache = smem; p.ccache_bits = bits; smem += 8 << bits; }
@@ -370,8 +459,7 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
     plan->grid = (int)grid;
     // big ranges per warp: 6 (measured on C5 / C1 at 1.8e7 .. 1.35e8 walkers with the guided tail below:
     // 4..8 within 1 % on the large launches, 6 best on the mid-size one; NRW_RANGES_PER_WARP overrides)
-    const char* rpw_env = getenv("NRW_RANGES_PER_WARP");
-    const long long rpw = rpw_env && atoll(rpw_env) > 0 ? atoll(rpw_env) : 6;
+    const long long rpw = e->cfg.ranges_per_warp;
     long long range = n / (grid * (WALK_THREADS / 32) * rpw);
     range = (range / 32) * 32;
     if (range < 32) range = 32;
@@ -391,8 +479,7 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
     if ((tl == TL_SCORE || tl == TL_HIST_S || tl == (TL_SCORE | TL_HIST_S)) && !w->score_sq && w->nt >= 2 &&
         tab_compact(tab)) {
         const bool hist = (tl & TL_HIST_S) != 0;
-        const char* force = getenv("NRW_K1");
-        bool general = force && strcmp(force, "general") == 0;
+        bool general = e->cfg.k1_general != 0;
         const bool idw = p.cwpack == 0x03020100u;
         {   // the trimmed kernel keeps 32-bit running sums per lane (see below): walks so long that even a
             // 32-id range could wrap them stay with the general kernel
@@ -400,8 +487,7 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
             if (!idw) for (int i = 0; i < 4; ++i) mw = std::max(mw, (long long)((p.cwpack >> (8 * i)) & 0xffu));
             if (32ll * (long long)w->nt * mw >= (1ll << 31)) general = true;
         }
-        const char* det_env = getenv("NRW_DET");             // NRW_DET=0: draw on deterministic rows too
-        const bool det = !(det_env && strcmp(det_env, "0") == 0);
+        const bool det = e->cfg.det != 0;                    // NRW_DET=0: draw on deterministic rows too
         if (!general) {
             // a lane's 32-bit step and score sums are flushed at every range fetch: keep
             // range * nt * (largest per-step weight) < 2^31
@@ -415,8 +501,7 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
             // one CTA of 1024 threads per SM.  NRW_CPS=2: two CTAs of 768 threads when the tables leave room
             // (48 instead of 32 warps per SM) -- +1.5 % before the range sizes were guided, 4-40 % slower
             // since (C1 mesh, 9e5 .. 1.35e8 walkers): more warps draw more tickets for no gain in issue rate
-            const char* cps_env = getenv("NRW_CPS");
-            const int cps = (plan->smem <= 112 * 1024 && cps_env && strcmp(cps_env, "2") == 0) ? 2 : 1;
+            const int cps = (plan->smem <= 112 * 1024 && e->cfg.cps == 2) ? 2 : 1;
 #define Y(TAB, IDW, DET, CPS)                                                       \
     if (tab == TAB && idw == IDW && det == DET && cps == CPS) {                     \
         if (hist) {                                                                 \
@@ -447,10 +532,8 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
     }
     {   // guided range sizes (fetch_range, walk_philox.cuh).  NRW_RANGE_TAIL / NRW_TAIL_RANGES override
         // (0 ranges = one size)
-        const char* rt_env = getenv("NRW_RANGE_TAIL");
-        const char* tr_env = getenv("NRW_TAIL_RANGES");
         const long long warps = (long long)plan->grid * (plan->block / 32);
-        p.n_phase = guided_phases(n, p.range, warps, rt_env ? atoll(rt_env) : 1024, tr_env ? atoll(tr_env) : 2,
+        p.n_phase = guided_phases(n, p.range, warps, e->cfg.range_tail, e->cfg.tail_ranges,
                                   p.ph_start, p.ph_ticket, p.ph_range);
     }
     if (!plan->fn)
@@ -472,14 +555,27 @@ extern "C" int nrw_walk_philox_plan(nrw_engine* e, const nrw_tables* t, const nr
     return NRW_OK;
 }
 
+// opt a kernel in to `smem` bytes of dynamic shared memory once (the attribute call costs microseconds per launch)
+static int ensure_smem(nrw_engine* e, const void* fn, int smem) {
+    std::lock_guard<std::mutex> lock(e->mu);
+    auto it = e->smem_attr.find(fn);
+    if (it != e->smem_attr.end() && it->second >= smem) return NRW_OK;
+    CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    e->smem_attr[fn] = smem;
+    return NRW_OK;
+}
+
 extern "C" int nrw_walk_philox(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, void* stream) {
     WalkPlan plan;
-    const int rc = make_plan(e, t, w, &plan);
+    int rc = make_plan(e, t, w, &plan);
     if (rc) return rc;
-    if (w->walker_hi == w->walker_lo) return NRW_OK;
+    if (w->walker_hi == w->walker_lo && !w->reduce) return NRW_OK;
     CUDA_TRY(cudaSetDevice(e->device));
-    CUDA_TRY(cudaFuncSetAttribute(plan.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, plan.smem));
-    CUDA_TRY(cudaMemsetAsync(e->work_next, 0, sizeof(unsigned long long), (cudaStream_t)stream));
+    if ((rc = ensure_smem(e, plan.fn, plan.smem))) return rc;
+    // this launch's ticket slot {work_next, done}: zero when free; the launch's last CTA zeroes it again
+    unsigned long long* slot = e->slots + 2 * (e->next_slot.fetch_add(1) % NRW_TICKET_SLOTS);
+    plan.p.work_next = slot;
+    plan.p.tail.done = slot + 1;
     void* args[] = {&plan.p};
     CUDA_TRY(cudaLaunchKernel(plan.fn, dim3(plan.grid), dim3(plan.block), args, plan.smem,
                               (cudaStream_t)stream));
@@ -525,28 +621,39 @@ static int grow(void** buf, size_t* cap, size_t need) {
 extern "C" int nrw_fluence_scores_host(nrw_engine* e, int32_t n_rows, int32_t n_live, int32_t n_alias,
                                        const void* rowinfo_host, const void* alias_host,
                                        int32_t n_starts, const int32_t* start_nodes_host,
-                                       const int64_t* start_prefix_host, int64_t walker_lo,
-                                       int64_t walker_hi, uint64_t seed, int32_t nt,
+                                       const int64_t* start_prefix_host, const int64_t* start_id_base_host,
+                                       int64_t walker_lo, int64_t walker_hi, uint64_t seed, int32_t nt,
                                        const double class_value[4], int64_t* score_host,
-                                       unsigned long long* counters_host, void* stream) {
+                                       unsigned long long* counters_host, const nrw_reduce* reduce, void* stream) {
     if (!e || !rowinfo_host || !alias_host || !start_nodes_host || !start_prefix_host || !score_host ||
         !class_value || n_rows <= 0 || n_alias <= 0 || n_starts <= 0)
         return fail(NRW_EINVAL, "nrw_fluence_scores_host: bad argument");
+    const long long n_tally = (long long)n_starts + NRW_N_COUNTERS;
+    if (reduce && (reduce->n != n_tally || !reduce->own_buf || (reduce->world > 1 && !reduce->out)))
+        return fail(NRW_EINVAL, "nrw_fluence_scores_host: reduce->n must be n_starts + %d", NRW_N_COUNTERS);
     cudaStream_t st = (cudaStream_t)stream;
+    std::lock_guard<std::mutex> lock(e->mu_host);              // the staging buffers below are per engine
     CUDA_TRY(cudaSetDevice(e->device));
-    const size_t rb = ((size_t)n_rows * 8 + 15) & ~(size_t)15, ab = ((size_t)n_alias * 8 + 15) & ~(size_t)15;
     int rc;
-    if ((rc = grow(&e->d_rowinfo, &e->cap_rowinfo, rb))) return rc;
-    if ((rc = grow(&e->d_alias, &e->cap_alias, ab))) return rc;
+    if ((rc = grow(&e->d_rowinfo, &e->cap_rowinfo, (size_t)n_rows * 8 + 16))) return rc;
+    if ((rc = grow(&e->d_alias, &e->cap_alias, (size_t)n_alias * 8 + 16))) return rc;
     if ((rc = grow(&e->d_starts, &e->cap_starts, (size_t)n_starts * 4))) return rc;
     if ((rc = grow(&e->d_prefix, &e->cap_prefix, (size_t)(n_starts + 1) * 8))) return rc;
-    if ((rc = grow(&e->d_score, &e->cap_score, (size_t)n_starts * 8))) return rc;
+    if (start_id_base_host && (rc = grow(&e->d_idbase, &e->cap_idbase, (size_t)n_starts * 8))) return rc;
     CUDA_TRY(cudaMemcpyAsync(e->d_rowinfo, rowinfo_host, (size_t)n_rows * 8, cudaMemcpyHostToDevice, st));
     CUDA_TRY(cudaMemcpyAsync(e->d_alias, alias_host, (size_t)n_alias * 8, cudaMemcpyHostToDevice, st));
     CUDA_TRY(cudaMemcpyAsync(e->d_starts, start_nodes_host, (size_t)n_starts * 4, cudaMemcpyHostToDevice, st));
     CUDA_TRY(cudaMemcpyAsync(e->d_prefix, start_prefix_host, (size_t)(n_starts + 1) * 8, cudaMemcpyHostToDevice, st));
-    CUDA_TRY(cudaMemsetAsync(e->d_score, 0, (size_t)n_starts * 8, st));
-    CUDA_TRY(cudaMemsetAsync(e->d_counters, 0, NRW_N_COUNTERS * sizeof(unsigned long long), st));
+    if (start_id_base_host)
+        CUDA_TRY(cudaMemcpyAsync(e->d_idbase, start_id_base_host, (size_t)n_starts * 8, cudaMemcpyHostToDevice, st));
+    long long* tally;                                           // scores, then the counters: one buffer
+    if (reduce) {
+        tally = (long long*)reduce->own_buf + reduce->offset;  // zeroed by the tail of the previous launch
+    } else {
+        if ((rc = grow(&e->d_tally, &e->cap_tally, (size_t)n_tally * 8))) return rc;
+        tally = (long long*)e->d_tally;
+        CUDA_TRY(cudaMemsetAsync(tally, 0, (size_t)n_tally * 8, st));
+    }
     nrw_tables t;
     memset(&t, 0, sizeof(t));
     t.n_rows = n_rows; t.n_live = n_live; t.alias_layout = NRW_ALIAS_COMPACT; t.n_alias = n_alias;
@@ -555,8 +662,9 @@ extern "C" int nrw_fluence_scores_host(nrw_engine* e, int32_t n_rows, int32_t n_
     memset(&w, 0, sizeof(w));
     w.n_starts = n_starts; w.start_nodes = (const int32_t*)e->d_starts;
     w.start_prefix = (const int64_t*)e->d_prefix;
+    w.start_id_base = start_id_base_host ? (const int64_t*)e->d_idbase : nullptr;
     w.walker_lo = walker_lo; w.walker_hi = walker_hi; w.seed = seed; w.nt = nt;
-    w.sampler = NRW_SAMPLER_ALIAS; w.score = (int64_t*)e->d_score;
+    w.sampler = NRW_SAMPLER_ALIAS; w.score = (int64_t*)tally;
     {   // weights of classes no row carries are free: if the used ones equal the class index, pass the
         // identity vector so that the walk takes the IDW kernel (walk_score.cuh)
         uint32_t present = 0;
@@ -566,13 +674,20 @@ extern "C" int nrw_fluence_scores_host(nrw_engine* e, int32_t n_rows, int32_t n_
         for (uint32_t c = 0; c < 4; ++c) if ((present >> c) & 1u) ident = ident && class_value[c] == (double)c;
         for (int i = 0; i < 4; ++i) w.class_value[i] = ident ? (double)i : class_value[i];
     }
-    w.counters = e->d_counters;
+    w.counters = (unsigned long long*)(tally + n_starts);
+    w.reduce = reduce;
     if ((rc = nrw_walk_philox(e, &t, &w, stream))) return rc;
-    CUDA_TRY(cudaMemcpyAsync(score_host, e->d_score, (size_t)n_starts * 8, cudaMemcpyDeviceToHost, st));
-    if (counters_host)
-        CUDA_TRY(cudaMemcpyAsync(counters_host, e->d_counters, NRW_N_COUNTERS * sizeof(unsigned long long),
+    const long long* result = (reduce && reduce->world > 1) ? (const long long*)reduce->out : tally;
+    CUDA_TRY(cudaMemcpyAsync(score_host, result, (size_t)n_starts * 8, cudaMemcpyDeviceToHost, st));
+    long long tail_host[NRW_N_COUNTERS + 1] = {0};             // counters (+ the exchange's status word)
+    const bool want_status = reduce && reduce->world > 1;
+    if (counters_host || want_status)
+        CUDA_TRY(cudaMemcpyAsync(tail_host, result + n_starts, (size_t)(NRW_N_COUNTERS + (want_status ? 1 : 0)) * 8,
                                  cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaStreamSynchronize(st));
+    if (counters_host) memcpy(counters_host, tail_host, NRW_N_COUNTERS * sizeof(unsigned long long));
+    if (want_status && tail_host[NRW_N_COUNTERS] != 0)
+        return fail(NRW_ECUDA, "nrw_fluence_scores_host: a peer did not reach the reduction within 5 s");
     return NRW_OK;
 }
 
@@ -585,13 +700,17 @@ extern "C" int nrw_p2p_allreduce_i64(nrw_engine* e, int64_t* out, const void* pe
         world > 64 || rank < 0 || rank >= world || epoch == 0)
         return fail(NRW_EINVAL, "nrw_p2p_allreduce_i64: bad argument");
     CUDA_TRY(cudaSetDevice(e->device));
-    long long grid = (n + P2P_THREADS - 1) / P2P_THREADS;
-    if (grid > 16) grid = 16;                                    // 80 KB per peer: latency-, not bandwidth-bound
-    const long long timeout_cycles = (long long)e->clock_khz * 1000ll * 5ll;   // 5 s without a peer: give up
-    p2p_allreduce_i64_kernel<<<(int)grid, P2P_THREADS, 0, (cudaStream_t)stream>>>(
-        (long long*)out, (const long long* const*)peer_bufs_dev, (unsigned long long* const*)peer_flags_dev,
-        (long long)offset, (long long)zero_offset, (long long)n, rank, world, (unsigned long long)epoch,
-        timeout_cycles, err_flag);
+    TailParams r;
+    memset(&r, 0, sizeof(r));
+    r.world = world; r.rank = rank;
+    r.bufs = (const long long* const*)peer_bufs_dev;
+    r.flags = (unsigned long long* const*)peer_flags_dev;
+    r.own = nullptr;                                            // resolved on the device: bufs[rank]
+    r.off = offset; r.zero_off = zero_offset; r.n = n; r.epoch = epoch;
+    r.out = (long long*)out; r.status = nullptr;
+    r.timeout_ns = 5000000000ull;                               // 5 s without a peer: give up
+    // 80 KB per peer: latency-, not bandwidth-bound -- one CTA issues every peer's loads at once
+    p2p_allreduce_i64_kernel<<<1, P2P_THREADS, 0, (cudaStream_t)stream>>>(r, err_flag);
     CUDA_TRY(cudaGetLastError());
     return NRW_OK;
 }
@@ -615,7 +734,7 @@ extern "C" int nrw_microbench(nrw_engine* e, int32_t kind, int32_t n, int32_t it
         default: return fail(NRW_EINVAL, "nrw_microbench: kind=%d", kind);
     }
     if (smem > e->max_smem) return fail(NRW_ENOSPC, "nrw_microbench: %d B of shared memory", smem);
-    CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem > 0 ? smem : 16));
+    if (int rc = ensure_smem(e, fn, smem > 0 ? smem : 16)) return rc;
     const uint2* tab = (const uint2*)table;
     void* args[] = {&n, &iters, &tab, &hist, &scratch};
     CUDA_TRY(cudaLaunchKernel(fn, dim3(grid), dim3(1024), args, smem, st));

@@ -23,10 +23,11 @@
 #include <type_traits>
 
 #include "common.cuh"
+#include "walk_tail.cuh"
 
 namespace nrw {
 
-enum : int { TAB_SMEM = 0, TAB_HYB = 1, TAB_GLB = 2, TAB_CDF = 3, TAB_FAC = 4 };
+enum : int { TAB_SMEM = 0, TAB_HYB = 1, TAB_GLB = 2, TAB_CDF = 3, TAB_FAC = 4, TAB_TREE = 5 };
 // compact alias tables (patterns in shared memory, paired draws); they differ in where a row's descriptor
 // comes from: shared memory (SMEM), global memory / L2 (HYB), or derived from three small shared-memory
 // tables on meshes with the (direction, cell) structure of the fluence matrix (FAC, fac_row below)
@@ -39,6 +40,7 @@ struct WalkParams {
     int n_rows, n_live, n_alias;
     const int32_t* indptr; const int32_t* cols; const double* cum; const uint8_t* node_class;
     const void* rowinfo; const void* alias;
+    const uint8_t* tree; const int32_t* tree_ptr;   // TAB_TREE: 8-bit Bernoulli thresholds in heap order per row
     int n_starts; const int32_t* start_nodes; const long long* start_prefix; const long long* start_id_base;
     long long lo, hi;
     uint32_t key; int nt;
@@ -49,7 +51,8 @@ struct WalkParams {
     unsigned long long* node_hist;
     uint32_t* count_tn; int t_cap; int per_start; int cnt_bins; int cnt_match;
     unsigned long long* counters;
-    unsigned long long* work_next; long long range;
+    unsigned long long* work_next; long long range;   // work_next: the launch's ticket counter (a slot of the engine's ring)
+    TailParams tail;                             // last-CTA work: slot reset, zeroing, the fused all-reduce (walk_tail.cuh)
     // guided range sizes (walk_score.cuh, fetch_range below): phase j hands out ids
     // [lo + ph_start[j], lo + ph_start[j+1]) in ranges of ph_range[j], tickets ph_ticket[j] .. ph_ticket[j+1]-1
     int n_phase;
@@ -59,6 +62,9 @@ struct WalkParams {
     // CTA-level cache of hot (t, node) bins in front of the global time-resolved counts: 2^ccache_bits
     // (tag, count) slots at sm_ccache; 0 bits = off
     int sm_ccache, ccache_bits;
+    // most likely trajectory of every start (nrw_walk.count_path): walkers still on it are tallied through a per-CTA
+    // histogram of the steps at which walkers LEAVE it (sm_left: n_starts x (t_cap + 1)); path staged at sm_path
+    const int32_t* cnt_path; int sm_path, sm_left;
     // TAB_FAC (tables.py::FactoredRows): live row k = i + j * fac_period; sources of the staged tables
     const void* fac_dir; const void* fac_tail; const void* fac_cls;
     int fac_period, fac_cells, fac_n_tail, fac_shift;
@@ -131,7 +137,7 @@ __device__ __forceinline__ int locate_start(const WalkParams& p, long long g) {
 }
 
 template <int TAB>
-struct RowRegs { uint32_t a, b, c, d; };   // COMPACT: a=w0 b=w1 | WIDE: off,n,base,cls | CDF: a=k b=n d=cls
+struct RowRegs { uint32_t a, b, c, d; };   // COMPACT: a=w0 b=w1 | WIDE: off,n,base,cls | CDF: a=k b=n d=cls | TREE: a=k b=n c=tree offset d=cls
 
 template <int TAB>
 __device__ __forceinline__ RowRegs<TAB> load_row(const WalkParams& p, const uint2* rowinfo_s, int k) {
@@ -152,6 +158,7 @@ __device__ __forceinline__ RowRegs<TAB> load_row(const WalkParams& p, const uint
         r.a = (uint32_t)k;
         r.b = (k < p.n_live) ? (uint32_t)(__ldg(p.indptr + k + 1) - __ldg(p.indptr + k)) : 0u;
         r.c = 0;
+        if constexpr (TAB == TAB_TREE) r.c = (uint32_t)__ldg(p.tree_ptr + k);
         r.d = p.node_class ? (uint32_t)__ldg(p.node_class + k) : 0u;
     }
     return r;
@@ -232,6 +239,14 @@ walk_philox_kernel(const __grid_constant__ WalkParams p) {
     if constexpr (TL & TL_CNT_G)
         if (p.ccache_bits)
             for (int i = tid; i < (1 << p.ccache_bits); i += WALK_THREADS) ccache_s[i] = make_uint2(0u, 0u);
+    int32_t* path_s = reinterpret_cast<int32_t*>(smem + p.sm_path);
+    uint32_t* left_s = reinterpret_cast<uint32_t*>(smem + p.sm_left);
+    const bool use_path = (TL & TL_CNT_G) && p.cnt_path != nullptr;
+    if constexpr (TL & TL_CNT_G)
+        if (use_path) {
+            for (int i = tid; i < p.n_starts * p.t_cap; i += WALK_THREADS) path_s[i] = __ldg(p.cnt_path + i);
+            for (int i = tid; i < p.n_starts * (p.t_cap + 1); i += WALK_THREADS) left_s[i] = 0u;
+        }
     if constexpr (kStage) mbar_wait(bar, 0);
     __syncthreads();
 
@@ -253,6 +268,7 @@ walk_philox_kernel(const __grid_constant__ WalkParams p) {
     RowRegs<TAB> srow{0, 0, 0, 0};
     long long acc = 0; double acc2 = 0.0;
     uint32_t nsteps = 0, nsurv = 0, novf = 0, sinkc = 0;
+    bool onpath = false;                // TL_CNT_G with count_path: the walker has followed its start's likely path so far
     // warp-uniform: the warp's current id range is [rbase + cur, rbase + end)
     long long rbase = 0;
     uint32_t cur = 0, end = 0;
@@ -325,6 +341,7 @@ walk_philox_kernel(const __grid_constant__ WalkParams p) {
                 c0 = (uint32_t)sid;
                 chi = (uint32_t)(sid >> 32) << 24;
                 t = t_init; x = 0;
+                onpath = true;
                 nsurv += surv_init;
             }
         }
@@ -346,6 +363,19 @@ walk_philox_kernel(const __grid_constant__ WalkParams p) {
                 if constexpr (!PAIRED) r = philox2x32_10(c0, chi | (uint32_t)t, key);
                 if constexpr (TAB == TAB_CDF) {
                     knew = sample_cdf(p.indptr, p.cols, p.cum, (int)row.a, u53(r.x, r.y));
+                } else if constexpr (TAB == TAB_TREE) {
+                    // the probability circuit of loihirw/rw_core.py:11-156: one Bernoulli neuron per tree level,
+                    // firing probability quantised to the 8-bit weight 128 p + 36 (here: threshold floor(128 p))
+                    unsigned long long bits = (unsigned long long)r.x | ((unsigned long long)r.y << 32);
+                    const int depth = row.b > 1u ? 32 - __clz((int)row.b - 1) : 0;
+                    uint32_t node = 0;
+                    for (int l = 0; l < depth; ++l) {
+                        const uint32_t thr = __ldg(p.tree + row.c + node);
+                        node = 2u * node + (((uint32_t)bits & 127u) < thr ? 1u : 2u);
+                        bits >>= 7;
+                    }
+                    const uint32_t leaf = min(node - ((1u << depth) - 1u), row.b - 1u);
+                    knew = __ldg(p.cols + __ldg(p.indptr + (int)row.a) + (int)leaf);
                 } else if constexpr (TAB == TAB_GLB) {
                     const uint32_t slot = __umulhi(r.x, row.b);
                     const uint4 e = __ldg(reinterpret_cast<const uint4*>(p.alias) + row.a + slot);
@@ -401,7 +431,23 @@ walk_philox_kernel(const __grid_constant__ WalkParams p) {
                 if (stepped) {
                     if (t < p.t_cap) bin = (gq * p.t_cap + t) * (long long)p.n_rows + knew; else ++novf;
                 }
-                if (p.ccache_bits) {
+                if (use_path) {
+                    // Walkers of one start move almost in lock step along the start's most likely trajectory, so
+                    // its (t, node) bins would take most tallies (contended atomics).  A walker still ON the path
+                    // is not tallied step by step: when it leaves the path at step L (first step off it, the step
+                    // after its death, or t_cap) ONE shared-memory atomic records L, and the epilogue credits the
+                    // path bins 1 .. L-1 from the suffix sums of that histogram -- the same counts exactly.
+                    if (stepped && onpath) {
+                        const int tc = t < p.t_cap ? t : p.t_cap;
+                        if (t >= p.t_cap || knew != path_s[s * p.t_cap + t]) {
+                            atomicAdd(left_s + s * (p.t_cap + 1) + tc, 1u);
+                            onpath = false;
+                        } else {
+                            bin = -1;                                  // on the path: credited in the epilogue
+                        }
+                    }
+                    if (bin >= 0) atomicAdd(p.count_tn + bin, 1u);      // off the path: diffuse bins, plain RED
+                } else if (p.ccache_bits) {
                     // Walkers of one start node move almost in lock step, so a few (t, node) bins take
                     // most of the tallies and global atomics on them serialise in L2.  Lanes of a warp on
                     // the same bin are merged by a vote; the merged count goes to a per-CTA shared-memory
@@ -434,6 +480,11 @@ walk_philox_kernel(const __grid_constant__ WalkParams p) {
                 const bool absorbed = row_n<TAB>(row) == 0u;
                 if (absorbed || t >= t_last) {
                     if (!absorbed) ++nsurv;
+                    if constexpr (TL & TL_CNT_G)
+                        if (use_path && onpath) {                      // died on the path at step t: credited through t
+                            atomicAdd(left_s + s * (p.t_cap + 1) + min(t + 1, p.t_cap), 1u);
+                            onpath = false;
+                        }
                     t = -1;
                     if constexpr (TL & TL_SCORE) {
                         acc += (long long)x;
@@ -471,6 +522,20 @@ walk_philox_kernel(const __grid_constant__ WalkParams p) {
         if (v4) atomicAdd(p.counters + 4, v4);
     }
     if constexpr (TL & TL_CNT_G) {
+        if (use_path) {
+            // walkers on the path at step tau = those that left it later: suffix sums of the leave-time histogram
+            __syncthreads();
+            for (int sidx = tid; sidx < p.n_starts; sidx += WALK_THREADS) {
+                const long long gq = p.per_start ? sidx : 0;
+                unsigned long long on = left_s[sidx * (p.t_cap + 1) + p.t_cap];
+                for (int tau = p.t_cap - 1; tau >= 1; --tau) {
+                    const int node = path_s[sidx * p.t_cap + tau];
+                    if (on && node >= 0)
+                        atomicAdd(p.count_tn + (gq * p.t_cap + tau) * (long long)p.n_rows + node, (uint32_t)on);
+                    on += left_s[sidx * (p.t_cap + 1) + tau];
+                }
+            }
+        }
         if (p.ccache_bits) {
             __syncthreads();
             for (int i = tid; i < (1 << p.ccache_bits); i += WALK_THREADS) {
@@ -492,6 +557,7 @@ walk_philox_kernel(const __grid_constant__ WalkParams p) {
                 if (h) atomicAdd(p.count_tn + i, h);
             }
     }
+    walk_tail(p.tail, p.work_next);
 }
 
 }  // namespace nrw

@@ -331,6 +331,7 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
             if (h) atomicAdd(p.node_hist + i, (unsigned long long)h);
         }
     }
+    walk_tail(p.tail, p.work_next);
 }
 
 }  // namespace nrw

@@ -100,7 +100,7 @@ def pc_tempdata(csr, neuraltime, initial_walkers, n_out_rows, rng=None, sampler=
         t_cap = min(nt, 1024)
         while True:
             res = eng.walk(tabs, [place], [amount], nt, seed, sampler=sampler, count_tn=True,
-                           t_cap=t_cap)
+                           t_cap=t_cap, count_path=True)
             if res.counters_dict()["t_overflow"] == 0 or t_cap >= nt:
                 break
             t_cap = min(nt, t_cap * 8)       # same seed -> same trajectories, longer tally window
@@ -145,7 +145,8 @@ def multi_source_tempdata(csr, neuraltime, initial_walkers, n_out_rows, rng=None
         seed = philox_seed_from_global_stream()
         t_cap = min(nt, 1024)
         while True:
-            res = eng.walk(tabs, nodes, counts, nt, seed, sampler=sampler, count_tn=True, t_cap=t_cap)
+            res = eng.walk(tabs, nodes, counts, nt, seed, sampler=sampler, count_tn=True, t_cap=t_cap,
+                           count_path=True)
             if res.counters_dict()["t_overflow"] == 0 or t_cap >= nt:
                 break
             t_cap = min(nt, t_cap * 8)

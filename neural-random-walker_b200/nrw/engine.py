@@ -21,7 +21,7 @@ LIB_PATH = os.path.join(_HERE, "csrc", "libnrw.so")
 
 NRW_N_COUNTERS = 8
 COUNTER_NAMES = ("steps", "exits", "survivors", "t_overflow", "walkers")
-SAMPLER = {"alias": 0, "cdf": 1}
+SAMPLER = {"alias": 0, "cdf": 1, "tree": 2}
 ALIAS_LAYOUT = {"none": 0, "compact": 1, "wide": 2}
 
 
@@ -38,7 +38,17 @@ class _Tables(C.Structure):
                 ("fac_dir", C.c_void_p), ("fac_tail", C.c_void_p), ("fac_cls", C.c_void_p),
                 ("fac_period", C.c_int32), ("fac_cells", C.c_int32), ("fac_n_tail", C.c_int32),
                 ("fac_shift", C.c_int32), ("fac_magic", C.c_uint32), ("fac_exit_w0", C.c_uint32),
-                ("fac_exit_base", C.c_uint32)]
+                ("fac_exit_base", C.c_uint32),
+                ("tree", C.c_void_p), ("tree_ptr", C.c_void_p)]
+
+
+class _Reduce(C.Structure):
+    """nrw_reduce (include/nrw.h): the fused all-reduce / next-buffer zeroing a walk runs in its tail."""
+    _fields_ = [("rank", C.c_int32), ("world", C.c_int32),
+                ("peer_bufs_dev", C.c_void_p), ("peer_flags_dev", C.c_void_p),
+                ("own_buf", C.c_void_p),
+                ("offset", C.c_int64), ("zero_offset", C.c_int64), ("n", C.c_int64),
+                ("epoch", C.c_uint64), ("out", C.c_void_p)]
 
 
 class _Walk(C.Structure):
@@ -50,7 +60,9 @@ class _Walk(C.Structure):
                 ("class_value", C.c_double * 4), ("time_weight", C.c_void_p),
                 ("node_hist", C.c_void_p),
                 ("count_tn", C.c_void_p), ("t_cap", C.c_int32), ("count_per_start", C.c_int32),
-                ("counters", C.c_void_p)]
+                ("counters", C.c_void_p),
+                ("count_path", C.c_void_p),
+                ("reduce", C.POINTER(_Reduce))]
 
 
 class _Replay(C.Structure):
@@ -64,7 +76,7 @@ class _Replay(C.Structure):
 _lib = None
 
 # every symbol include/nrw.h declares; tests/test_capi.py checks the library exports them all
-EXPORTS = ("nrw_abi_version", "nrw_last_error", "nrw_create", "nrw_destroy", "nrw_device_info",
+EXPORTS = ("nrw_abi_version", "nrw_last_error", "nrw_create", "nrw_destroy", "nrw_device_info", "nrw_engine_config",
            "nrw_build_cum", "nrw_walk_philox", "nrw_walk_philox_plan", "nrw_walk_replay",
            "nrw_assemble_events", "nrw_expand_events", "nrw_expand_counts",
            "nrw_fluence_scores_host", "nrw_microbench", "nrw_p2p_allreduce_i64", "nrw_guided_phases")
@@ -86,6 +98,7 @@ def load_library():
     lib.nrw_create.argtypes = [C.c_int, C.POINTER(vp)]
     lib.nrw_destroy.argtypes = [vp]
     lib.nrw_device_info.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    lib.nrw_engine_config.argtypes = [vp, C.c_char_p, C.c_int]
     lib.nrw_build_cum.argtypes = [vp, i32, vp, vp, vp, vp]
     lib.nrw_walk_philox.argtypes = [vp, C.POINTER(_Tables), C.POINTER(_Walk), vp]
     lib.nrw_walk_philox_plan.argtypes = [vp, C.POINTER(_Tables), C.POINTER(_Walk), C.c_char_p,
@@ -95,8 +108,8 @@ def load_library():
     lib.nrw_assemble_events.argtypes = [vp, i32, vp, vp, vp, vp, vp, vp, dbl, dbl, vp, i32, i32, vp, vp]
     lib.nrw_expand_events.argtypes = [vp, i64, vp, vp, vp, i32, i32, vp, vp]
     lib.nrw_expand_counts.argtypes = [vp, vp, i32, i32, i32, i32, i64, vp, vp]
-    lib.nrw_fluence_scores_host.argtypes = [vp, i32, i32, i32, vp, vp, i32, vp, vp, i64, i64, u64,
-                                            i32, C.POINTER(dbl * 4), vp, vp, vp]
+    lib.nrw_fluence_scores_host.argtypes = [vp, i32, i32, i32, vp, vp, i32, vp, vp, vp, i64, i64, u64,
+                                            i32, C.POINTER(dbl * 4), vp, vp, C.POINTER(_Reduce), vp]
     lib.nrw_microbench.argtypes = [vp, i32, i32, i32, vp, vp, vp, vp]
     lib.nrw_p2p_allreduce_i64.argtypes = [vp, vp, vp, vp, i64, i64, i64, i32, i32, u64, vp, vp]
     lib.nrw_guided_phases.argtypes = [i64, i64, i64, i64, i64, vp, vp, vp, C.POINTER(i32)]
@@ -138,6 +151,8 @@ class DeviceTables:
     struct: _Tables
     max_class: int = 0          # largest source class any row carries (weights of unused classes are free)
     factored: tuple = ()        # device tensors of the factored row descriptors (tables.FactoredRows), if any
+    tree: tuple = ()            # (thresholds uint8, tree_ptr int32) device tensors of the tree sampler, built on demand
+    tree_host: tuple = ()
 
     @property
     def n_rows(self):
@@ -202,9 +217,13 @@ class PreparedWalk:
 
 
 class Engine:
-    """One engine per (process, device).  All launches go to torch's current stream."""
+    """One engine per (process, device).  All launches go to torch's current stream.
 
-    def __init__(self, device=None):
+    ``switches`` (measurement / test only): NRW_* environment switches this engine is
+    created with -- the library reads them once, in nrw_create, so an A/B tool or a parity test that wants
+    another code path creates another engine: ``Engine(0, switches={"NRW_DET": "0"})``."""
+
+    def __init__(self, device=None, switches=None):
         import torch
         self.torch = torch
         self.lib = load_library()
@@ -215,11 +234,27 @@ class Engine:
             device = torch.cuda.current_device()
         self.device = torch.device("cuda", device if isinstance(device, int) else device.index)
         h = C.c_void_p()
-        self._check(self.lib.nrw_create(self.device.index, C.byref(h)))
+        saved = {k: os.environ.get(k) for k in (switches or {})}
+        try:
+            for k, v in (switches or {}).items():
+                if v is None:
+                    os.environ.pop(k, None)
+                else:
+                    os.environ[k] = str(v)
+            self._check(self.lib.nrw_create(self.device.index, C.byref(h)))
+        finally:
+            for k, v in saved.items():
+                if v is None:
+                    os.environ.pop(k, None)
+                else:
+                    os.environ[k] = v
         self.handle = h
         a, b = C.c_int(), C.c_int()
         self._check(self.lib.nrw_device_info(self.handle, C.byref(a), C.byref(b)))
         self.n_sms, self.max_smem = a.value, b.value
+        buf = C.create_string_buffer(256)
+        self._check(self.lib.nrw_engine_config(self.handle, buf, 256))
+        self.config = buf.value.decode()
 
     def close(self):
         if getattr(self, "handle", None):
@@ -362,17 +397,33 @@ class Engine:
             res.count_tn = torch.zeros((groups, t_cap, tables.n_rows), dtype=torch.int32, device=self.device)
             res.t_cap = t_cap
             w.count_tn, w.t_cap, w.count_per_start = _ptr(res.count_tn), t_cap, int(bool(count_per_start))
+            if count_path and n_starts * t_cap <= (1 << 13):
+                # most likely trajectory of every start (include/nrw.h, nrw_walk.count_path): walkers still on
+                # it are tallied through a leave-time histogram instead of one contended atomic per step
+                keep["path"] = self._dev(_tables.likely_paths(tables.csr, start_nodes, t_cap), np.int32)
+                w.count_path = _ptr(keep["path"])
         return w, res, keep
+
+    def _ensure_tree(self, tables: DeviceTables):
+        """Tree-sampler tables (loihirw.rw_core probability circuit, 8-bit weights) -- built and uploaded on first use."""
+        if not tables.tree:
+            thr, ptr = _tables.build_tree_tables(tables.csr)
+            tables.tree_host = (thr, ptr)
+            tables.tree = (self._dev(thr if len(thr) else np.zeros(1, np.uint8), np.uint8), self._dev(ptr, np.int32))
+            tables.struct.tree, tables.struct.tree_ptr = _ptr(tables.tree[0]), _ptr(tables.tree[1])
 
     def walk(self, tables: DeviceTables, start_nodes, start_counts, nt, seed, *, walker_range=None,
              sampler="alias", score=False, score_sq=False, class_value=None, time_weight=None,
              node_hist=False, count_tn=False, t_cap=None, count_per_start=False,
-             start_id_base=None) -> WalkResult:
+             start_id_base=None, count_path=False) -> WalkResult:
         """One K1 launch on the current stream.  Walker g (global id over the concatenated start
         list) starts on its start node; ``walker_range`` restricts the launch to ids [lo, hi)."""
+        if sampler == "tree":
+            self._ensure_tree(tables)
         w, res, keep = self._walk_struct(tables, start_nodes, start_counts, nt, seed, walker_range,
                                          sampler, score, score_sq, class_value, time_weight,
-                                         node_hist, count_tn, t_cap, count_per_start, start_id_base)
+                                         node_hist, count_tn, t_cap, count_per_start, start_id_base,
+                                         count_path=count_path)
         name = C.create_string_buffer(96)
         self._check(self.lib.nrw_walk_philox_plan(self.handle, C.byref(tables.struct), C.byref(w), name,
                                                   96, None, None, None))
@@ -386,7 +437,7 @@ class Engine:
         launches K1 again (what bench.py times: no host-side table or descriptor work per step)."""
         args = dict(walker_range=None, sampler="alias", score=False, score_sq=False, class_value=None,
                     time_weight=None, node_hist=False, count_tn=False, t_cap=None, count_per_start=False,
-                    start_id_base=None, counters=None)
+                    start_id_base=None, counters=None, count_path=False)
         args.update(kw)
         w, res, keep = self._walk_struct(tables, start_nodes, start_counts, nt, seed, **args)
         name = C.create_string_buffer(96)
@@ -545,24 +596,32 @@ class Engine:
                                          walker_hi, nt, class_value, score_out, counters_out)(seed)
 
     def prepare_fluence_scores_host(self, alias_tables, n_rows, n_live, start_nodes, start_prefix, walker_lo,
-                                    walker_hi, nt, class_value, score_out, counters_out):
+                                    walker_hi, nt, class_value, score_out, counters_out, start_id_base=None,
+                                    exchange=None):
         """The same call with its arguments converted once: returns ``solve(seed)`` for a loop of solves
         over the same buffers (a CUDA-graph replay of the copy / walk / copy-back sequence was measured
-        and gave nothing: the per-call cost beyond the kernel, ~50 us, is DMA and synchronisation latency)."""
+        and gave nothing: the per-call cost beyond the kernel, ~50 us, is DMA and synchronisation latency).
+        ``exchange`` (nrw.dist.TallyExchange, N > 1): the walk tallies into the exchange's buffer and sums it
+        over ranks in its own tail; the reduced scores come back to ``score_out``."""
         if alias_tables.layout != "compact":
             raise NrwError("the host entry takes the compact alias layout")
+        if exchange is not None and not exchange.fused:
+            raise NrwError("the host entry needs the fused exchange (peer memory on every rank)")
         cv = (C.c_double * 4)(*[float(x) for x in class_value])
-        keep = (alias_tables.rowinfo, alias_tables.alias, start_nodes, start_prefix, score_out, counters_out, cv)
+        keep = (alias_tables.rowinfo, alias_tables.alias, start_nodes, start_prefix, score_out, counters_out, cv,
+                start_id_base, exchange)
         fn, check, handle, stream = self.lib.nrw_fluence_scores_host, self._check, self.handle, self.stream
         head = (handle, int(n_rows), int(n_live), int(alias_tables.n_alias),
                 C.c_void_p(alias_tables.rowinfo.ctypes.data), C.c_void_p(alias_tables.alias.ctypes.data),
                 len(start_nodes), C.c_void_p(start_nodes.ctypes.data), C.c_void_p(start_prefix.ctypes.data),
+                C.c_void_p(start_id_base.ctypes.data) if start_id_base is not None else None,
                 int(walker_lo), int(walker_hi))
-        tail = (int(nt), C.byref(cv), C.c_void_p(score_out.ctypes.data),
-                C.c_void_p(counters_out.ctypes.data) if counters_out is not None else None, stream)
+        mid = (int(nt), C.byref(cv), C.c_void_p(score_out.ctypes.data),
+               C.c_void_p(counters_out.ctypes.data) if counters_out is not None else None)
 
         def solve(seed):
-            check(fn(*head, int(seed) & 0xFFFFFFFFFFFFFFFF, *tail))
+            red = exchange.arm()[1] if exchange is not None else None
+            check(fn(*head, int(seed) & 0xFFFFFFFFFFFFFFFF, *mid, red, stream))
         solve.keepalive = keep
         return solve
 

@@ -347,3 +347,68 @@ def classify_source(srcvals: np.ndarray, n_rows: int):
         node_class[:len(srcvals)][srcvals == x] = ci
         class_value[ci] = x
     return node_class, class_value
+
+
+def likely_paths(csr: TransitionCSR, start_nodes, t_cap: int) -> np.ndarray:
+    """int32 [n_starts, t_cap]: the most likely trajectory of every start -- path[s, 0] = the start node,
+    path[s, t] = the most probable successor of path[s, t-1] (first one on ties), -1 once the path has reached an
+    absorbing row.  Walkers of one start move along it almost in lock step (the fluence matrix keeps a walker's
+    direction with probability 1 - pone, fluence_mini_app.py:368-371), which is what makes the time-resolved
+    tally contended; the walk tallies walkers on this path through a leave-time histogram instead
+    (include/nrw.h, nrw_walk.count_path).  Any choice of path gives the same counts; the most likely one removes
+    the most atomics."""
+    start_nodes = np.asarray(start_nodes, dtype=np.int64).reshape(-1)
+    path = np.full((len(start_nodes), int(t_cap)), -1, dtype=np.int32)
+    path[:, 0] = start_nodes
+    main: dict = {}
+
+    def successor(r: int) -> int:
+        if r < 0 or r >= csr.n_live:
+            return -1
+        hit = main.get(r)
+        if hit is None:
+            lo, hi = int(csr.indptr[r]), int(csr.indptr[r + 1])
+            hit = main[r] = int(csr.cols[lo + int(np.argmax(csr.vals[lo:hi]))]) if hi > lo else -1
+        return hit
+    for t in range(1, int(t_cap)):
+        for s in range(len(start_nodes)):
+            path[s, t] = successor(int(path[s, t - 1]))
+    return path
+
+
+def build_tree_tables(csr: TransitionCSR):
+    """The reference's probability circuit (loihirw/rw_core.py:11-156) as a sampler table: for every row the
+    firing thresholds floor(128 * p) of its binary tree of Bernoulli neurons -- the 8-bit weights ``128*p + 36`` of
+    rw_core.py:151-153 without their offset -- in heap order (root first).  Returns (thresholds uint8[total],
+    tree_ptr int32[n_rows + 1]); row r owns n2(r) - 1 entries, n2 = next power of two of its fan-out.  Rows are
+    de-duplicated by their probabilities while building (a fluence mesh has a few dozen patterns)."""
+    from loihirw.rw_core import build_tree
+    lens = csr.row_lengths().astype(np.int64)
+    lens[csr.n_live:] = 0
+    if lens.max(initial=0) > 512:
+        raise ValueError("the tree sampler spends 7 bits per level of one 64-bit draw: rows of <= 512 entries")
+    n2 = np.where(lens > 1, 1 << np.ceil(np.log2(np.maximum(lens, 2))).astype(np.int64), 1)
+    ptr = np.zeros(csr.n_rows + 1, dtype=np.int64)
+    ptr[1:] = np.cumsum(n2 - 1)
+    thr = np.zeros(int(ptr[-1]), dtype=np.uint8)
+    seen: dict = {}
+    for r in range(csr.n_live):
+        n = int(lens[r])
+        if n <= 1:
+            continue
+        vals = csr.vals[csr.indptr[r]:csr.indptr[r + 1]]
+        key = vals.tobytes()
+        heap = seen.get(key)
+        if heap is None:
+            _, fire_p, _, _, _ = build_tree(list(vals))       # neurons level by level, leaves' parents first, root last
+            q = np.floor(128.0 * fire_p + 36.0) - 36.0         # the programmed weight, offset removed: floor(128 p)
+            m = int(n2[r])
+            heap = np.zeros(m - 1, dtype=np.uint8)
+            at, width = 0, m // 2
+            while width >= 1:                                  # level with `width` neurons sits at heap [width-1, 2*width-1)
+                heap[width - 1:2 * width - 1] = q[at:at + width]
+                at += width
+                width //= 2
+            seen[key] = heap
+        thr[ptr[r]:ptr[r + 1]] = heap
+    return thr, ptr.astype(np.int32)

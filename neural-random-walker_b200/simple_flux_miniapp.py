@@ -55,10 +55,11 @@ run_functions = {'fugu': run_fugu, 'loihi': run_loihi, 'spinnaker': run_spinnake
 
 
 def _counts_pc_fused(csr, M, nt, n_cols, rng, sampler):
-    """Occupancy counts [start state, state, t < n_cols] for both start states in one pass."""
+    """Occupancy counts [start state, state, t < n_cols] for both start states in one pass; state 2 = walkers
+    absorbed AT step t (the sink row of the 3-state chain, simple_flux_miniapp.py:197-201)."""
     eng, tabs = dropin.device_tables(csr)
     mode = dropin.resolve_rng(rng, 2 * int(M))
-    td = np.zeros((2, 2, n_cols))
+    td = np.zeros((2, 3, n_cols))
     if mode == "replay":
         # the reference walks until every walker is absorbed or nt is reached (:189); so does replay,
         # which keeps the global stream position identical
@@ -69,7 +70,7 @@ def _counts_pc_fused(csr, M, nt, n_cols, rng, sampler):
         c = rep.ev_count[:rep.n_events].cpu().numpy()
         for s in (0, 1):
             sl = slice(int(off[s]), int(off[s + 1]))
-            keep = (k[sl] < 2) & (t[sl] < n_cols)
+            keep = (k[sl] < 3) & (t[sl] < n_cols)
             td[s, k[sl][keep], t[sl][keep]] = c[sl][keep]
         return td, rep.draws_used, mode
     seed = ndist.broadcast_int(dropin.philox_seed_from_global_stream())
@@ -81,7 +82,7 @@ def _counts_pc_fused(csr, M, nt, n_cols, rng, sampler):
                    t_cap=nt_k, count_per_start=True, start_id_base=[lo, int(M) + lo])
     ndist.allreduce_sum_([res.count_tn, res.counters])
     cnt = res.count_tn.cpu().numpy()          # [2, t_cap, 3]
-    td[:, :, :nt_k] = np.transpose(cnt[:, :, :2], (0, 2, 1))
+    td[:, :, :nt_k] = np.transpose(cnt[:, :, :3], (0, 2, 1))
     td[0, 0, 0] = M
     td[1, 1, 0] = M
     return td, res.counters_dict()["steps"], mode
@@ -126,6 +127,14 @@ def run(args):
                                            args.get('sampler', 'alias'))
         for i in range(meshSize):
             rwSol[i, :maxT] = (initp * td[i, 0, :maxT] + initn * td[i, 1, :maxT]) / M   # :327
+        if args['use_sinks']:
+            # the reference's pc path ignores --use_sinks (Q14); here it ALSO returns the walkers absorbed at every
+            # step -- next to rwSol, never inside it: sinks[i, t] for start state i, kept in
+            # ``last_sink_counts`` and written to <results stem>_sinks.csv
+            global last_sink_counts
+            last_sink_counts = td[:, 2, :maxT].copy()
+            if rank == 0:
+                np.savetxt(os.path.splitext(results_filename)[0] + "_sinks.csv", last_sink_counts, delimiter=",")
         el = time.time() - t0
         rw_logger.info('    2 mesh points, {} walker-steps, rng={} in {:.4f} s'.format(steps, mode, el))
     else:
@@ -151,6 +160,9 @@ def run(args):
         np.savetxt(results_filename, rwSol, delimiter=",")                    # :358
         rw_logger.info("Solution saved to {}".format(results_filename))
     return rwSol
+
+
+last_sink_counts = None     # float64 [2, maxT]: walkers absorbed at each step per start state (--use_sinks, pc mode)
 
 
 def true_solution(args, maxT):

@@ -65,3 +65,23 @@ def occupancy_expectation(indptr, cols, vals, n_rows, n_live, start_dist, nt):
         cur = QT @ live
         out[t] = cur
     return out
+
+
+def fluence_error_stats(per_start, mean, var, M, unit, min_expected_count=50.0):
+    """"fluence err vs pc ref" (BASELINE.json metric) of one Philox-mode solve against the exact M -> infinity
+    limit of the reference's chain: relative L2 over all cells, and the per-cell z statistics
+    |rwSol - E| / sqrt(Var/M) over the cells whose expected tally M * E / unit is at least
+    ``min_expected_count`` (below that the tally is a small count, not a normal variable; those cells stay in
+    the L2 figure).  ``unit`` = rwSol units per tallied hit (v * dt * S0).  Cells with zero variance must be
+    reproduced exactly."""
+    per_start, mean, var = (np.asarray(a, dtype=np.float64) for a in (per_start, mean, var))
+    sigma = np.sqrt(var / float(M))
+    exact = sigma == 0
+    test = (~exact) & (float(M) * mean / float(unit) >= min_expected_count)
+    z = np.abs(per_start[test] - mean[test]) / sigma[test]
+    return {"M": int(M), "rel_l2": float(np.linalg.norm(per_start - mean) / np.linalg.norm(mean)),
+            "max_abs_z": float(z.max()) if z.size else 0.0,
+            "frac_within_3sigma": float((z < 3.0).mean()) if z.size else 1.0,
+            "cells": int(per_start.size), "cells_z_tested": int(test.sum()),
+            "zero_variance_cells_exact": bool(np.array_equal(per_start[exact], mean[exact])),
+            "expected_rel_l2": float(np.sqrt(var.sum() / float(M)) / np.linalg.norm(mean))}

@@ -63,7 +63,7 @@ def _decode_alias(at):
 
 def walk_port(csr, start_nodes, start_counts, nt, seed, *, alias=None, cum=None, node_class=None,
               sampler="alias", walker_range=None, class_value=None, time_weight=None, t_cap=None,
-              count_per_start=False, start_id_base=None):
+              count_per_start=False, start_id_base=None, tree=None):
     """Simulate every walker of walk_philox.cuh; returns a dict with the same tallies:
     score[n_starts] (int64), score_sq[n_starts] (float64, summed in id order -- compare with
     tolerance), node_hist[n_rows], count_tn[groups, t_cap, n_rows], counters."""
@@ -114,6 +114,21 @@ def walk_port(csr, start_nodes, start_counts, nt, seed, *, alias=None, cum=None,
             slot = ((r0.astype(np.uint64) * nrow[kk].astype(np.uint64)) >> np.uint64(32)).astype(np.int64)
             e = off[kk] + slot
             knew = base[kk] + np.where(r1 <= th[e], aa[e], bb[e])
+        elif sampler == "tree":
+            # walk_philox.cuh TAB_TREE: 7 bits per level of (r0 | r1 << 32), left iff u7 < threshold (heap order)
+            thr, ptr = tree
+            bits = r0.astype(np.uint64) | (r1.astype(np.uint64) << np.uint64(32))
+            n = nrow[kk]
+            depth = np.where(n > 1, np.ceil(np.log2(np.maximum(n, 2))).astype(np.int64), 0)
+            node = np.zeros(len(idx), np.int64)
+            for l in range(int(depth.max(initial=0))):
+                act = depth > l
+                t7 = thr[np.minimum(ptr[kk].astype(np.int64) + node, max(len(thr) - 1, 0))].astype(np.int64)
+                fire = (bits & np.uint64(127)).astype(np.int64) < t7
+                node = np.where(act, 2 * node + np.where(fire, 1, 2), node)
+                bits = bits >> np.uint64(7)
+            leaf = np.minimum(node - ((1 << depth) - 1), n - 1)
+            knew = csr.cols[csr.indptr[kk] + leaf].astype(np.int64)
         else:
             u = u53(r0, r1)
             knew = np.empty(len(idx), np.int64)

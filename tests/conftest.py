@@ -35,10 +35,33 @@ def pytest_collection_modifyitems(config, items):
             it.add_marker(skip)
 
 
+SWITCHES = ("NRW_K1", "NRW_DET", "NRW_TAB", "NRW_CPS", "NRW_RANGES_PER_WARP", "NRW_RANGE_TAIL", "NRW_TAIL_RANGES",
+            "NRW_CNT_MATCH", "NRW_CNT_CACHE", "NRW_CNT_PATH")
+
+
+class _EnginePerSwitches:
+    """The library reads its NRW_* measurement switches once, in nrw_create (include/nrw.h).  Parity tests pick a
+    code path with ``monkeypatch.setenv("NRW_...")`` and then call ``engine.walk(...)``: this proxy hands every
+    call to an engine created under the switches in force at that moment (one engine per combination; device
+    tables are plain device pointers and serve every engine of the device)."""
+
+    def __init__(self):
+        self._engines = {}
+
+    def _current(self):
+        from nrw.engine import Engine, get_engine
+        key = tuple(os.environ.get(k) for k in SWITCHES)
+        if key not in self._engines:
+            self._engines[key] = get_engine() if not any(key) else Engine(0)
+        return self._engines[key]
+
+    def __getattr__(self, name):
+        return getattr(self._current(), name)
+
+
 @pytest.fixture(scope="session")
 def engine():
-    from nrw.engine import get_engine
-    return get_engine()
+    return _EnginePerSwitches()
 
 
 @pytest.fixture(scope="session")

@@ -54,4 +54,9 @@ def test_reference_arm_runs_on_the_host_and_prints_one_json_line():
         assert k in d, k
     assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["e2e"]["d2h_bytes_per_step"] == 0
     assert d["e2e"]["value"] == d["value"] and d["cpu_baseline"]["value"] == d["value"]
-    assert d["cpu_baseline"]["cores"] >= 1 and d["cpu_baseline"]["kind"] == "port"
+    # the reference itself where a copy is reachable (this container), the oracle's port of it elsewhere (GPU box)
+    have_ref = os.path.isfile("/root/reference/fluence_mini_app.py")
+    assert d["cpu_baseline"]["cores"] >= 1 and d["cpu_baseline"]["kind"] == ("reference" if have_ref else "port")
+    # the arm describes the workload IT ran (the reference's M, nt and RNG), not the GPU arm's
+    assert "M=100" in d["config"]["workload"] and "MT19937" in d["config"]["workload"]
+    assert d["config"]["workers"] == d["cpu_baseline"]["cores"]

@@ -31,7 +31,7 @@ def test_library_exports_every_declared_symbol():
     for s in _declared_symbols():
         assert hasattr(lib, s), "libnrw.so does not export %s" % s
     assert set(_declared_symbols()) == set(engine.EXPORTS)
-    assert lib.nrw_abi_version() == 2
+    assert lib.nrw_abi_version() == 3
 
 
 def test_struct_mirrors_match_header_field_order():
@@ -39,7 +39,7 @@ def test_struct_mirrors_match_header_field_order():
     from nrw import engine
     text = re.sub(r"/\*.*?\*/", "", open(HEADER).read(), flags=re.S)
     for cname, mirror in (("nrw_tables", engine._Tables), ("nrw_walk", engine._Walk),
-                          ("nrw_replay", engine._Replay)):
+                          ("nrw_replay", engine._Replay), ("nrw_reduce", engine._Reduce)):
         body = re.search(r"typedef struct %s \{(.*?)\} %s;" % (cname, cname), text, re.S).group(1)
         fields = []
         for decl in body.split(";"):

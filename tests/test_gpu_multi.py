@@ -70,3 +70,16 @@ def test_p2p_score_allreduce_equals_nccl(p2p, n):
     env = dict(os.environ, NRW_P2P_REDUCE=p2p, NRW_TEST_N=n)
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, env=env)
     assert r.returncode == 0 and "p2p_reduce_worker ok p2p=%s" % (p2p == "1") in r.stdout, (r.stdout[-1500:], r.stderr[-3000:])
+
+
+@pytest.mark.skipif(not _two_gpus(), reason="needs 2 GPUs")
+@pytest.mark.parametrize("p2p", ["1", "0"])
+def test_fused_walk_exchange_two_ranks(p2p):
+    """The walk's tail sums over ranks (nrw_walk.reduce): equal to dist.all_reduce and to the unsharded walk, through
+    TallyExchange, solve_fluence and the host entry; p2p = 0: the logged NCCL fall-back."""
+    worker = os.path.join(os.path.dirname(os.path.abspath(__file__)), "fused_exchange_worker.py")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+           "--master-addr", "127.0.0.1", "--master-port", str(29671 + int(p2p)), worker]
+    env = dict(os.environ, NRW_P2P_REDUCE=p2p)
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=400, env=env)
+    assert r.returncode == 0 and "fused_exchange_worker ok p2p=%s" % (p2p == "1") in r.stdout, (r.stdout[-1500:], r.stderr[-3000:])

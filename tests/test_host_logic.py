@@ -312,3 +312,44 @@ def test_factorise_rows_is_exact_or_absent():
     at = tables.build_alias(csr)
     at.rowinfo[100, 1] += 30
     assert tables.factorise_rows(at, csr.n_live) is None
+
+
+def test_likely_paths_follow_the_most_probable_successor(c1_csr):
+    from nrw import tables
+    path = tables.likely_paths(c1_csr, [435, 900, 14], 12)
+    assert path.shape == (3, 12) and path[0, 0] == 435 and (path[1, 1:] == -1).all() and path[1, 0] == 900
+    for s in range(3):
+        for t in range(1, 12):
+            prev = path[s, t - 1]
+            if prev < 0 or prev >= c1_csr.n_live:
+                assert path[s, t] == -1
+                continue
+            lo, hi = c1_csr.indptr[prev], c1_csr.indptr[prev + 1]
+            assert path[s, t] == c1_csr.cols[lo + np.argmax(c1_csr.vals[lo:hi])]
+
+
+def test_tree_sampler_tables_realise_the_quantised_probability_circuit(c1_csr):
+    """nrw.tables.build_tree_tables (the device table of sampler='tree') against loihirw.rw_core: walking the heap of
+    8-bit thresholds with exact 7-bit uniforms gives tree_distribution(quantise=True) for every row pattern."""
+    from loihirw import rw_core
+    from nrw import tables
+    thr, ptr = tables.build_tree_tables(c1_csr)
+    lens = c1_csr.row_lengths()
+    assert ptr[-1] == len(thr) and (np.diff(ptr)[lens <= 1] == 0).all()
+    for r in (0, 14, 15, 435, 449, 885):
+        n = int(lens[r])
+        if n <= 1:
+            continue
+        lo, hi = c1_csr.indptr[r], c1_csr.indptr[r + 1]
+        n2 = 1 << int(np.ceil(np.log2(n)))
+        heap = thr[ptr[r]:ptr[r + 1]].astype(np.float64) / 128.0
+        assert len(heap) == n2 - 1
+        prob = np.ones(n2)                                   # exact distribution of the heap walk
+        for leaf in range(n2):
+            node = leaf + n2 - 1
+            while node > 0:
+                parent = (node - 1) // 2
+                prob[leaf] *= heap[parent] if node == 2 * parent + 1 else 1.0 - heap[parent]
+                node = parent
+        want = rw_core.tree_distribution(list(c1_csr.vals[lo:hi]), quantise=True)
+        assert np.allclose(prob, want, atol=1e-15) and prob[n:].sum() == 0

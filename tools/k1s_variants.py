@@ -40,10 +40,11 @@ def main():
                 configs.append(("rpw%d_min%d_x%d" % (rpw, rt, tr), {"NRW_RANGES_PER_WARP": str(rpw), "NRW_RANGE_TAIL": str(rt),
                                                                      "NRW_TAIL_RANGES": str(tr)}))
     for tag, env in configs:
-        for k in knobs:
-            os.environ.pop(k, None)
-        os.environ.update(env)
-        launch, res = eng.prepare_walk(tabs, starts, M, 30000, seed=1, score=True, class_value=[0, 1, 0, 0])
+        # the library reads its switches once per engine: one engine per variant (device tables are shared)
+        sw = {k: None for k in knobs}
+        sw.update(env)
+        ev_eng = Engine(0, switches=sw)
+        launch, res = ev_eng.prepare_walk(tabs, starts, M, 30000, seed=1, score=True, class_value=[0, 1, 0, 0])
         for _ in range(3):
             launch()
         ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(10)]

@@ -1,6 +1,12 @@
 #!/usr/bin/env python
 """Summarise an .ncu-rep (read here, no GPU): key raw metrics per launch and the hot SASS lines.
-Usage: python tools/ncu_summary.py gpurun_out/prof.ncu-rep [--sass] [--min-share 0.002]"""
+Usage: python tools/ncu_summary.py gpurun_out/prof.ncu-rep [--sass] [--min-share 0.002]
+       python tools/ncu_summary.py prof.ncu-rep --traffic-json profiles/walk_traffic.json --bench-line bench.json
+           --source "profiles/<summary>.txt (...)" --round 2
+The second form regenerates profiles/walk_traffic.json -- the per-launch facts of the dominant kernel that
+bench.py's roofline object is built from (warp-instructions, lanes per instruction, DRAM bytes, pipe use) -- from
+the capture, and takes the walker-steps per launch from the bench line of the SAME command, so that bench.py can
+refuse a capture of another kernel or workload."""
 import csv
 import io
 import subprocess
@@ -31,10 +37,64 @@ def run(args):
     return subprocess.run(["ncu", "-i"] + args, capture_output=True, text=True).stdout
 
 
+TAB_NAMES = {0: "TAB_SMEM", 1: "TAB_HYB", 2: "TAB_GLB", 3: "TAB_CDF", 4: "TAB_FAC", 5: "TAB_TREE"}
+
+
+def plan_name(ncu_name):
+    """ncu's demangled kernel name -> the planner's name (nrw_walk_philox_plan), e.g.
+    walk_score_kernel<0, 1, 1, 1, 0> -> walk_score<TAB_SMEM,true,true,cps=1>."""
+    import re
+    m = re.search(r"walk_score_kernel<\(?(?:int\))?(\d+), \(?(?:bool\))?(\d+), \(?(?:bool\))?(\d+), \(?(?:int\))?(\d+), \(?(?:bool\))?(\d+)>", ncu_name)
+    if m:
+        tab, idw, det, cps, hist = (int(x) for x in m.groups())
+        return "%s<%s,%s,%s,cps=%d>" % ("walk_score_hist" if hist else "walk_score", TAB_NAMES[tab],
+                                        "true" if idw else "false", "true" if det else "false", cps)
+    m = re.search(r"walk_philox_kernel<\(?(?:int\))?(\d+), \(?(?:int\))?(\d+)>", ncu_name)
+    if m:
+        return "walk_philox<%s,%d>" % (TAB_NAMES[int(m.group(1))], int(m.group(2)))
+    return ncu_name
+
+
+def traffic_json(h, data, out_path, argv):
+    import json
+    r = data[0]
+    val = lambda k: float(r[h.index(k)].replace(",", "")) if k in h and r[h.index(k)] not in ("", "n/a") else None
+    unit_scale = {"Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "byte": 1.0}
+    def bytes_of(k, units):
+        v = val(k)
+        return None if v is None else v * unit_scale.get(units[h.index(k)], 1.0)
+    units = argv["units"]
+    facts = {"kernel": plan_name(r[h.index("Kernel Name")]),
+             "dram_bytes_per_launch": (bytes_of("dram__bytes_read.sum", units) or 0.0) + (bytes_of("dram__bytes_write.sum", units) or 0.0),
+             "round": argv.get("round"), "source": argv.get("source"),
+             "ncu_kernel_us": (val("gpu__time_duration.sum") or 0.0) * {"ns": 1e-3, "us": 1.0, "ms": 1e3, "s": 1e6}.get(
+                 units[h.index("gpu__time_duration.sum")], 1.0),
+             "warp_inst_per_launch": val("smsp__inst_executed.sum"),
+             "threads_per_warp_inst": val("smsp__thread_inst_executed_per_inst_executed.ratio"),
+             "issue_active_pct": val("smsp__issue_active.avg.pct_of_peak_sustained_active"),
+             "alu_pipe_pct": val("sm__pipe_alu_cycles_active.avg.pct_of_peak_sustained_active"),
+             "fmaheavy_pipe_pct": val("sm__pipe_fmaheavy_cycles_active.avg.pct_of_peak_sustained_elapsed"),
+             "smsp_active_share_of_elapsed": (val("smsp__cycles_active.avg") or 0.0) / max(val("sm__cycles_elapsed.avg") or 1.0, 1.0),
+             "smem_bank_conflict_share": (val("l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum") or 0.0)
+                                         / max(val("l1tex__data_pipe_lsu_wavefronts_mem_shared.sum") or 1.0, 1.0)}
+    if argv.get("bench_line"):
+        line = json.loads(open(argv["bench_line"]).read().strip().splitlines()[-1])
+        facts["walker_steps_per_launch"] = int(line["roofline"]["walker_steps_per_launch"])
+        assert line["roofline"]["kernel"] == facts["kernel"], (line["roofline"]["kernel"], facts["kernel"])
+        facts["warp_inst_per_32_walker_steps"] = 32.0 * facts["warp_inst_per_launch"] / facts["walker_steps_per_launch"]
+    json.dump(facts, open(out_path, "w"), indent=1)
+    print("wrote", out_path, facts)
+
+
 def main():
     rep = sys.argv[1]
     rows = list(csv.reader(io.StringIO(run([rep, "--page", "raw", "--csv"]))))
     h, u, data = rows[0], rows[1], rows[2:]
+    if "--traffic-json" in sys.argv:
+        opt = lambda k: sys.argv[sys.argv.index(k) + 1] if k in sys.argv else None
+        traffic_json(h, data, opt("--traffic-json"), {"units": u, "bench_line": opt("--bench-line"), "source": opt("--source"),
+                                                       "round": int(opt("--round") or 0)})
+        return
     keys = KEYS + [k for k in h if k.startswith('smsp__average_warps_issue_stalled') and k.endswith('per_issue_active.ratio')]
     print("# kernel:", ' | '.join(r[h.index('Kernel Name')] for r in data))
     for k in keys:
