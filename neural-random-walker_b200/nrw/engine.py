@@ -330,7 +330,7 @@ class Engine:
     # ------------------------------------------------------------------ K1
     def _walk_struct(self, tables, start_nodes, start_counts, nt, seed, walker_range, sampler,
                      score, score_sq, class_value, time_weight, node_hist, count_tn, t_cap,
-                     count_per_start, start_id_base=None, counters=None):
+                     count_per_start, start_id_base=None, counters=None, count_path=False):
         torch = self.torch
         start_nodes = np.asarray(start_nodes, dtype=np.int64).reshape(-1)
         n_starts = len(start_nodes)

@@ -82,6 +82,6 @@ def fluence_error_stats(per_start, mean, var, M, unit, min_expected_count=50.0):
     return {"M": int(M), "rel_l2": float(np.linalg.norm(per_start - mean) / np.linalg.norm(mean)),
             "max_abs_z": float(z.max()) if z.size else 0.0,
             "frac_within_3sigma": float((z < 3.0).mean()) if z.size else 1.0,
-            "cells": int(per_start.size), "cells_z_tested": int(test.sum()),
+            "cells": int(per_start.size), "cells_z_tested": int(test.sum()), "cells_zero_variance": int(exact.sum()),
             "zero_variance_cells_exact": bool(np.array_equal(per_start[exact], mean[exact])),
             "expected_rel_l2": float(np.sqrt(var.sum() / float(M)) / np.linalg.norm(mean))}

@@ -24,7 +24,8 @@ C4 = dict(dt=0.001, da=1.0 / 63.0, v=200, SigS=0.15, L=1)
 
 def _check(stats, l2_max=None):
     assert stats["zero_variance_cells_exact"]
-    assert stats["cells_z_tested"] > 0.5 * stats["cells"] or stats["M"] < 20000, stats
+    # the z test covers nearly every cell that has a variance at all (exit-row starts are reproduced exactly)
+    assert stats["cells_z_tested"] > 0.9 * (stats["cells"] - stats["cells_zero_variance"]) or stats["M"] < 20000, stats
     assert stats["max_abs_z"] < 5.5, stats
     assert stats["frac_within_3sigma"] >= 0.995, stats
     assert stats["rel_l2"] < 1.5 * stats["expected_rel_l2"], stats

@@ -353,3 +353,25 @@ def test_tree_sampler_tables_realise_the_quantised_probability_circuit(c1_csr):
                 node = parent
         want = rw_core.tree_distribution(list(c1_csr.vals[lo:hi]), quantise=True)
         assert np.allclose(prob, want, atol=1e-15) and prob[n:].sum() == 0
+
+
+def test_launch_descriptors_build_without_a_device(c1_csr):
+    """The host half of Engine.walk / prepare_walk (start list, id bases, tally buffers, likely paths, tree tables,
+    the ctypes structs) on CPU tensors: everything up to the library call."""
+    import ctypes as C
+    import torch
+    from nrw import engine as E, tables
+    eng = E.Engine.__new__(E.Engine)
+    eng.torch, eng.device, eng.lib, eng.handle = torch, torch.device("cpu"), E.load_library(), None
+    tabs = E.DeviceTables(c1_csr, None, None, None, None, None, None, None, None, E._Tables())
+    w, res, keep = eng._walk_struct(tabs, [435, 14], [5, 7], 40, 3, None, "alias", True, True, [0, 1, 0, 0],
+                                    np.ones(40), True, True, 40, True, start_id_base=[0, 100], count_path=True)
+    assert w.n_starts == 2 and w.walker_hi == 12 and w.t_cap == 40 and w.count_per_start == 1
+    assert res.count_tn.shape == (2, 40, 901) and res.score.numel() == 2 and res.node_hist.numel() == 901
+    path = keep["path"].numpy()
+    assert path.shape == (2, 40) and path[0, 0] == 435 and np.array_equal(path, tables.likely_paths(c1_csr, [435, 14], 40))
+    assert w.count_path == keep["path"].data_ptr() and not w.reduce
+    eng._ensure_tree(tabs)
+    assert tabs.struct.tree == tabs.tree[0].data_ptr() and tabs.tree_host[1][-1] == len(tabs.tree_host[0])
+    with pytest.raises(E.NrwError):                      # the library refuses a NULL engine: no launch happened
+        eng.prepare_walk(tabs, [435], 5, 40, 3, score=True, class_value=[0, 1, 0, 0])

@@ -96,7 +96,8 @@ def c4d(M=20_000_000, nt=40):
     for rep in range(3):
         torch.cuda.synchronize()
         t0 = time.perf_counter()
-        res = eng.walk(tabs, starts, [M // len(starts)] * len(starts), nt, 50 + rep, count_tn=True, t_cap=nt)
+        res = eng.walk(tabs, starts, [M // len(starts)] * len(starts), nt, 50 + rep, count_tn=True, t_cap=nt,
+                       count_path=True)
         torch.cuda.synchronize()
         t_walk = time.perf_counter() - t0
     c = res.counters_dict()
