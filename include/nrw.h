@@ -127,16 +127,19 @@ typedef struct nrw_tables {
 /* ---- the path's one collective, fused into the walk (N > 1), and the zeroing of the next tally buffer ---
  * The per-start scores and the counters of a launch live in ONE int64 buffer per rank,
  * own_buf[offset, offset + n) (nrw_walk.score and nrw_walk.counters must point into it).  When the last
- * block of the launch retires it (world > 1) publishes `epoch` to every peer, waits for theirs, sums all
- * ranks' vectors over NVLink peer memory into out[0, n) and writes out[n] = 0 (1 if a peer did not arrive
- * within 5 s: the sums are then invalid and no buffer was zeroed -- test it per solve); then it zeroes
- * own_buf[zero_offset, zero_offset + n) (zero_offset < 0: nothing).  Callers alternate two halves of
- * own_buf by epoch parity (offset = (epoch & 1) * n', zero_offset = the other half): a half is zeroed only
- * after the wait of the following epoch, which proves that every peer has finished reading it, so one
- * signal / wait per solve suffices and no memset is ever launched.  world == 1: no exchange, `out` may be
- * NULL; the tail only zeroes the next half.  peer_bufs_dev / peer_flags_dev: DEVICE arrays of `world`
- * pointers -- every rank's buffer (int64) and flag array (uint64[world], zero-initialised) as mapped
- * into this process (symmetric memory / CUDA IPC; nrw/dist.py uses torch's symmetric-memory allocator);
+ * block of the launch retires it (world > 1) publishes `epoch` to every peer, waits for theirs, sums ITS SLICE
+ * (1 / world of the vector) over all ranks over NVLink peer memory, pushes the sums into every peer's
+ * own_buf[out_offset, out_offset + n) and signals / awaits "delivered"; the status word
+ * own_buf[out_offset + even(n)] is 0 afterwards, 1 if a peer did not arrive within 5 s (the sums are then invalid
+ * and no buffer was zeroed -- test it per solve).  It also zeroes own_buf[zero_offset, zero_offset + n)
+ * (zero_offset < 0: nothing).  Callers alternate two halves of own_buf by epoch parity (offset = the half of
+ * this epoch, zero_offset = the other half): a half is zeroed only after the first wait of the following epoch,
+ * which proves that every peer has finished reading it, so no memset is ever launched.  All offsets are even
+ * and the regions hold even(n) = (n + 1) & ~1 words (an odd n carries one pad word that stays zero);
+ * own_buf holds at least out_offset + even(n) + 2 words.  world == 1: no exchange; the tail only zeroes the next
+ * half and the result is own_buf[offset, offset + n) itself.  peer_bufs_dev / peer_flags_dev: DEVICE arrays
+ * of `world` pointers -- every rank's buffer (int64) and flag array (uint64[2 * world], zero-initialised) as
+ * mapped into this process (symmetric memory / CUDA IPC; nrw/dist.py uses torch's symmetric-memory allocator);
  * `epoch` > 0 and increases by one per launch on every rank.  Replaces the all-reduce a multi-process
  * run(args) of fluence_mini_app.py:397-438 needs once per solve.                                      */
 typedef struct nrw_reduce {
@@ -146,7 +149,7 @@ typedef struct nrw_reduce {
     int64_t* own_buf;
     int64_t  offset, zero_offset, n;
     uint64_t epoch;
-    int64_t* out;                   /* [n + 1] (device)                                  */
+    int64_t  out_offset;            /* where the sums over ranks land in own_buf (world > 1) */
 } nrw_reduce;
 
 typedef struct nrw_walk {
@@ -277,8 +280,8 @@ NRW_API int  nrw_expand_counts(nrw_engine* e, const uint32_t* count_tn, int32_t 
  * compact alias tables and the start list to the device, runs K1 in score mode, copies
  * score / counters back and synchronises `stream`.  `reduce` NULL: single GPU, the engine's own
  * tally buffer.  With `reduce` (N > 1; n must be n_starts + NRW_N_COUNTERS): the walk tallies into
- * reduce->own_buf + offset, the sums over ranks come back from reduce->out, and the call fails with
- * NRW_ECUDA if a peer timed out.  start_id_base_host may be NULL.                          */
+ * reduce->own_buf + offset, the sums over ranks come back from reduce->own_buf + out_offset, and the call
+ * fails with NRW_ECUDA if a peer timed out.  start_id_base_host may be NULL.                */
 NRW_API int  nrw_fluence_scores_host(nrw_engine* e,
                              int32_t n_rows, int32_t n_live, int32_t n_alias,
                              const void* rowinfo_host, const void* alias_host,
@@ -289,21 +292,15 @@ NRW_API int  nrw_fluence_scores_host(nrw_engine* e,
                              int64_t* score_host, unsigned long long* counters_host,
                              const nrw_reduce* reduce, void* stream);
 
-/* The path's one collective over peer memory (no NCCL): out[i] = sum over ranks q of
- * peer_bufs[q][offset + i].  peer_bufs_dev / peer_flags_dev are DEVICE arrays of `world` pointers:
- * every rank's score buffer (int64) and flag array (uint64[world], zero-initialised) as mapped into
- * this process (symmetric memory / CUDA IPC; nrw/dist.py uses torch's symmetric-memory allocator).
- * The kernel publishes `epoch` (> 0, increasing by one per call on every rank) to all peers, waits
- * for theirs, then reads and sums.  Alternate `offset` between two buffers per epoch: a buffer may be
- * rewritten once the NEXT call has been enqueued; zero_offset >= 0 makes the kernel zero this rank's
- * own buffer at that offset after the wait (the buffer of the next step), -1 leaves it.  *err_flag (device int) is set to 1 if a peer does
- * not arrive within 5 s (%globaltimer); `out` and the buffers are then left untouched.  The walk runs the same exchange in its own tail
- * (nrw_walk.reduce); this entry serves tallies no single walk launch produced.  Replaces the all-reduce a multi-process run(args) of
- * fluence_mini_app.py:397-438 needs once per solve. */
-NRW_API int  nrw_p2p_allreduce_i64(nrw_engine* e, int64_t* out, const void* peer_bufs_dev,
-                                   const void* peer_flags_dev, int64_t offset, int64_t zero_offset,
-                                   int64_t n, int32_t rank, int32_t world, uint64_t epoch,
-                                   int32_t* err_flag, void* stream);
+/* The path's one collective over peer memory (no NCCL) as a stand-alone launch: afterwards
+ * peer_bufs[q][out_offset + i] = sum over ranks r of peer_bufs[r][offset + i] on every rank q (i < n).  Same
+ * protocol, buffer layout and alternation rule as nrw_reduce above (the walk runs this exchange in its own tail;
+ * this entry serves tallies no single walk launch produced).  *err_flag (device int) is set to 1 if a peer does
+ * not arrive within 5 s (%globaltimer); the output region is then incomplete.  Replaces the all-reduce a
+ * multi-process run(args) of fluence_mini_app.py:397-438 needs once per solve. */
+NRW_API int  nrw_p2p_allreduce_i64(nrw_engine* e, const void* peer_bufs_dev, const void* peer_flags_dev,
+                                   int64_t offset, int64_t zero_offset, int64_t out_offset, int64_t n,
+                                   int32_t rank, int32_t world, uint64_t epoch, int32_t* err_flag, void* stream);
 
 /* Roofline denominators measured on the engine's device at the walk's own launch geometry (one
  * 1024-thread CTA per SM): kind 0 = random atomicAdd on a per-CTA shared-memory histogram of n bins,

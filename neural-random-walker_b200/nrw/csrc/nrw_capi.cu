@@ -117,7 +117,7 @@ extern "C" int nrw_create(int device, nrw_engine** out) {
     e->next_slot = 0;
     e->d_rowinfo = e->d_alias = e->d_starts = e->d_prefix = e->d_idbase = e->d_tally = nullptr;
     e->cap_rowinfo = e->cap_alias = e->cap_starts = e->cap_prefix = e->cap_idbase = e->cap_tally = 0;
-    const size_t slot_bytes = (size_t)NRW_TICKET_SLOTS * 2 * sizeof(unsigned long long);
+    const size_t slot_bytes = (size_t)NRW_TICKET_SLOTS * TICKET_WORDS * sizeof(unsigned long long);
     cudaError_t err = cudaMalloc(&e->slots, slot_bytes);
     if (err == cudaSuccess) err = cudaMemset(e->slots, 0, slot_bytes);
     if (err != cudaSuccess) {
@@ -337,8 +337,10 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
         if (r->world < 1 || r->world > 64 || r->rank < 0 || r->rank >= r->world || r->n <= 0 || r->offset < 0 ||
             !r->own_buf || r->epoch == 0)
             return fail(NRW_EINVAL, "nrw_walk_philox: bad reduce descriptor");
-        if (r->world > 1 && (!r->peer_bufs_dev || !r->peer_flags_dev || !r->out))
-            return fail(NRW_EINVAL, "nrw_walk_philox: reduce over %d ranks needs peer buffers, flags and out", r->world);
+        if (r->world > 1 && (!r->peer_bufs_dev || !r->peer_flags_dev || r->out_offset < 0))
+            return fail(NRW_EINVAL, "nrw_walk_philox: reduce over %d ranks needs peer buffers, flags and out_offset", r->world);
+        if (((r->offset | r->out_offset | (r->zero_offset < 0 ? 0 : r->zero_offset)) & 1) != 0)
+            return fail(NRW_EINVAL, "nrw_walk_philox: reduce offsets must be even (16-byte aligned halves)");
         const long long* lo = (const long long*)r->own_buf + r->offset;
         const long long* hi = lo + r->n;
         if (w->score && ((const long long*)w->score < lo || (const long long*)w->score + w->n_starts > hi))
@@ -346,13 +348,12 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
         if (w->counters && ((const long long*)w->counters < lo || (const long long*)w->counters + NRW_N_COUNTERS > hi))
             return fail(NRW_EINVAL, "nrw_walk_philox: counters are not inside the reduce buffer");
         p.tail.world = r->world; p.tail.rank = r->rank;
-        p.tail.bufs = (const long long* const*)r->peer_bufs_dev;
+        p.tail.bufs = (long long* const*)r->peer_bufs_dev;
         p.tail.flags = (unsigned long long* const*)r->peer_flags_dev;
         p.tail.own = (long long*)r->own_buf;
-        p.tail.off = r->offset; p.tail.zero_off = r->zero_offset; p.tail.n = r->n;
+        p.tail.off = r->offset; p.tail.zero_off = r->zero_offset; p.tail.out_off = r->out_offset; p.tail.n = r->n;
         p.tail.epoch = r->epoch;
-        p.tail.out = (long long*)r->out;
-        p.tail.status = r->out ? (long long*)r->out + r->n : nullptr;
+        p.tail.status = r->world > 1 ? (long long*)r->own_buf + r->out_offset + ((r->n + 1) & ~1ll) : nullptr;
     }
     if (w->count_tn && w->t_cap < 1) return fail(NRW_EINVAL, "nrw_walk_philox: t_cap=%d", w->t_cap);
     if (w->count_tn && w->walker_hi - w->walker_lo >= (1ll << 32))
@@ -572,10 +573,10 @@ extern "C" int nrw_walk_philox(nrw_engine* e, const nrw_tables* t, const nrw_wal
     if (w->walker_hi == w->walker_lo && !w->reduce) return NRW_OK;
     CUDA_TRY(cudaSetDevice(e->device));
     if ((rc = ensure_smem(e, plan.fn, plan.smem))) return rc;
-    // this launch's ticket slot {work_next, done}: zero when free; the launch's last CTA zeroes it again
-    unsigned long long* slot = e->slots + 2 * (e->next_slot.fetch_add(1) % NRW_TICKET_SLOTS);
+    // this launch's ticket slot (walk_tail.cuh): all zero when free; the launch's last tail CTA zeroes it again
+    unsigned long long* slot = e->slots + TICKET_WORDS * (e->next_slot.fetch_add(1) % NRW_TICKET_SLOTS);
     plan.p.work_next = slot;
-    plan.p.tail.done = slot + 1;
+    plan.p.tail.slot = slot;
     void* args[] = {&plan.p};
     CUDA_TRY(cudaLaunchKernel(plan.fn, dim3(plan.grid), dim3(plan.block), args, plan.smem,
                               (cudaStream_t)stream));
@@ -629,7 +630,7 @@ extern "C" int nrw_fluence_scores_host(nrw_engine* e, int32_t n_rows, int32_t n_
         !class_value || n_rows <= 0 || n_alias <= 0 || n_starts <= 0)
         return fail(NRW_EINVAL, "nrw_fluence_scores_host: bad argument");
     const long long n_tally = (long long)n_starts + NRW_N_COUNTERS;
-    if (reduce && (reduce->n != n_tally || !reduce->own_buf || (reduce->world > 1 && !reduce->out)))
+    if (reduce && (reduce->n != n_tally || !reduce->own_buf))
         return fail(NRW_EINVAL, "nrw_fluence_scores_host: reduce->n must be n_starts + %d", NRW_N_COUNTERS);
     cudaStream_t st = (cudaStream_t)stream;
     std::lock_guard<std::mutex> lock(e->mu_host);              // the staging buffers below are per engine
@@ -677,40 +678,44 @@ extern "C" int nrw_fluence_scores_host(nrw_engine* e, int32_t n_rows, int32_t n_
     w.counters = (unsigned long long*)(tally + n_starts);
     w.reduce = reduce;
     if ((rc = nrw_walk_philox(e, &t, &w, stream))) return rc;
-    const long long* result = (reduce && reduce->world > 1) ? (const long long*)reduce->out : tally;
+    const long long* result = (reduce && reduce->world > 1) ? (const long long*)reduce->own_buf + reduce->out_offset : tally;
     CUDA_TRY(cudaMemcpyAsync(score_host, result, (size_t)n_starts * 8, cudaMemcpyDeviceToHost, st));
-    long long tail_host[NRW_N_COUNTERS + 1] = {0};             // counters (+ the exchange's status word)
+    // counters (+ the exchange's status word: it follows the sums, after the pad word of an odd n -- n_tally is
+    // n_starts + 8, so the status sits at n_tally or n_tally + 1)
+    long long tail_host[NRW_N_COUNTERS + 2] = {0};
     const bool want_status = reduce && reduce->world > 1;
     if (counters_host || want_status)
-        CUDA_TRY(cudaMemcpyAsync(tail_host, result + n_starts, (size_t)(NRW_N_COUNTERS + (want_status ? 1 : 0)) * 8,
+        CUDA_TRY(cudaMemcpyAsync(tail_host, result + n_starts, (size_t)(NRW_N_COUNTERS + (want_status ? 2 : 0)) * 8,
                                  cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaStreamSynchronize(st));
     if (counters_host) memcpy(counters_host, tail_host, NRW_N_COUNTERS * sizeof(unsigned long long));
-    if (want_status && tail_host[NRW_N_COUNTERS] != 0)
+    if (want_status && tail_host[NRW_N_COUNTERS + (n_tally & 1)] != 0)
         return fail(NRW_ECUDA, "nrw_fluence_scores_host: a peer did not reach the reduction within 5 s");
     return NRW_OK;
 }
 
 // ---- the path's collective over peer memory ------------------------------------------------------
-extern "C" int nrw_p2p_allreduce_i64(nrw_engine* e, int64_t* out, const void* peer_bufs_dev,
-                                     const void* peer_flags_dev, int64_t offset, int64_t zero_offset,
-                                     int64_t n, int32_t rank, int32_t world, uint64_t epoch,
-                                     int32_t* err_flag, void* stream) {
-    if (!e || !out || !peer_bufs_dev || !peer_flags_dev || !err_flag || n <= 0 || offset < 0 || world < 1 ||
-        world > 64 || rank < 0 || rank >= world || epoch == 0)
+extern "C" int nrw_p2p_allreduce_i64(nrw_engine* e, const void* peer_bufs_dev, const void* peer_flags_dev,
+                                     int64_t offset, int64_t zero_offset, int64_t out_offset, int64_t n,
+                                     int32_t rank, int32_t world, uint64_t epoch, int32_t* err_flag, void* stream) {
+    if (!e || !peer_bufs_dev || !peer_flags_dev || !err_flag || n <= 0 || offset < 0 || out_offset < 0 || world < 1 ||
+        world > 64 || rank < 0 || rank >= world || epoch == 0 ||
+        ((offset | out_offset | (zero_offset < 0 ? 0 : zero_offset)) & 1) != 0)
         return fail(NRW_EINVAL, "nrw_p2p_allreduce_i64: bad argument");
     CUDA_TRY(cudaSetDevice(e->device));
     TailParams r;
     memset(&r, 0, sizeof(r));
     r.world = world; r.rank = rank;
-    r.bufs = (const long long* const*)peer_bufs_dev;
+    r.bufs = (long long* const*)peer_bufs_dev;
     r.flags = (unsigned long long* const*)peer_flags_dev;
     r.own = nullptr;                                            // resolved on the device: bufs[rank]
-    r.off = offset; r.zero_off = zero_offset; r.n = n; r.epoch = epoch;
-    r.out = (long long*)out; r.status = nullptr;
+    r.off = offset; r.zero_off = zero_offset; r.out_off = out_offset; r.n = n; r.epoch = epoch;
+    r.status = nullptr;
     r.timeout_ns = 5000000000ull;                               // 5 s without a peer: give up
-    // 80 KB per peer: latency-, not bandwidth-bound -- one CTA issues every peer's loads at once
-    p2p_allreduce_i64_kernel<<<1, P2P_THREADS, 0, (cudaStream_t)stream>>>(r, err_flag);
+    // 80 KB per peer: latency-, not bandwidth-bound -- one 16-byte pair per thread, every load in flight at once
+    long long grid = ((n + 1) / 2 + P2P_THREADS - 1) / P2P_THREADS;
+    if (grid > P2P_CTAS) grid = P2P_CTAS;
+    p2p_allreduce_i64_kernel<<<(int)grid, P2P_THREADS, 0, (cudaStream_t)stream>>>(r, err_flag);
     CUDA_TRY(cudaGetLastError());
     return NRW_OK;
 }

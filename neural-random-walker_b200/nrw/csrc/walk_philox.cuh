@@ -557,7 +557,7 @@ walk_philox_kernel(const __grid_constant__ WalkParams p) {
                 if (h) atomicAdd(p.count_tn + i, h);
             }
     }
-    walk_tail(p.tail, p.work_next);
+    walk_tail(p.tail);
 }
 
 }  // namespace nrw

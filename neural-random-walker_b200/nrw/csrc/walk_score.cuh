@@ -331,7 +331,7 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
             if (h) atomicAdd(p.node_hist + i, (unsigned long long)h);
         }
     }
-    walk_tail(p.tail, p.work_next);
+    walk_tail(p.tail);
 }
 
 }  // namespace nrw

@@ -68,9 +68,10 @@ def allreduce_sum_(tensors):
 
 
 class _SymmetricPair:
-    """Two alternating int64 tally buffers of ``n`` words (padded to an even count: 16-byte aligned halves) plus
-    a flag array, in torch's symmetric memory when every rank can map every peer (NVLink / NVSwitch box, NCCL
-    backend), else in plain device memory.  All ranks take the same decision (one MIN all-reduce); whenever the
+    """Two alternating int64 tally buffers of ``n`` words (padded to an even count: 16-byte aligned halves), the
+    output region the sums over ranks land in, a status word, and a flag array -- in torch's symmetric memory when
+    every rank can map every peer (NVLink / NVSwitch box, NCCL backend), else in plain device memory.  Layout (words):
+    [0, n_pad) half 0 | [n_pad, 2 n_pad) half 1 | [2 n_pad, 3 n_pad) sums | [3 n_pad] status.  All ranks take the same decision (one MIN all-reduce); whenever the
     peer-memory path is not taken on a multi-rank job the reason is logged once."""
 
     def __init__(self, n: int, engine):
@@ -81,7 +82,8 @@ class _SymmetricPair:
         self.rank, self.world = world()
         self.p2p = False
         dev = engine.device
-        self.bufs = torch.zeros(2 * self.n_pad, dtype=torch.int64, device=dev)
+        self.words = 3 * self.n_pad + 2
+        self.bufs = torch.zeros(self.words, dtype=torch.int64, device=dev)
         self.hb = self.hf = None
         if self.world > 1 and dist.is_initialized():
             ok, why = 0, ""
@@ -93,8 +95,8 @@ class _SymmetricPair:
                 try:
                     import torch.distributed._symmetric_memory as symm
                     group = dist.group.WORLD.group_name
-                    bufs = symm.empty(2 * self.n_pad, dtype=torch.int64, device=dev)
-                    flags = symm.empty(max(self.world, 8), dtype=torch.int64, device=dev)
+                    bufs = symm.empty(self.words, dtype=torch.int64, device=dev)
+                    flags = symm.empty(8 * max(self.world, 2), dtype=torch.int64, device=dev)   # 8 CTAs x world words (stand-alone kernel)
                     bufs.zero_()
                     flags.zero_()
                     hb = symm.rendezvous(bufs, group)
@@ -120,6 +122,17 @@ class _SymmetricPair:
     def half(self, h: int):
         return self.bufs[h * self.n_pad:h * self.n_pad + self.n]
 
+    @property
+    def out_offset(self):
+        return 2 * self.n_pad
+
+    def sums(self):
+        """int64[n] view of the region the exchange writes the sums over ranks into."""
+        return self.bufs[2 * self.n_pad:2 * self.n_pad + self.n]
+
+    def status(self):
+        return self.bufs[3 * self.n_pad:3 * self.n_pad + 1]
+
 
 class ScoreAllReduce:
     """The path's one collective as a STAND-ALONE step: the sum over ranks of an int64 tally vector as ONE kernel
@@ -137,7 +150,7 @@ class ScoreAllReduce:
         self.n, self.engine, self.torch = int(n), engine, torch
         self.rank, self.world = self.pair.rank, self.pair.world
         self.epoch = 0
-        self.out = torch.zeros(self.n, dtype=torch.int64, device=engine.device)
+        self.out = self.pair.sums()                       # the peers push their slices of the sums here
         self._err = torch.zeros(1, dtype=torch.int32, device=engine.device)
 
     @property
@@ -169,8 +182,8 @@ class ScoreAllReduce:
             other.zero_()
             return self.out
         e, pr = self.engine, self.pair
-        e._check(e.lib.nrw_p2p_allreduce_i64(e.handle, self.out.data_ptr(), pr.hb.buffer_ptrs_dev,
-                                             pr.hf.buffer_ptrs_dev, half * pr.n_pad, (half ^ 1) * pr.n_pad,
+        e._check(e.lib.nrw_p2p_allreduce_i64(e.handle, pr.hb.buffer_ptrs_dev, pr.hf.buffer_ptrs_dev,
+                                             half * pr.n_pad, (half ^ 1) * pr.n_pad, pr.out_offset,
                                              self.n, self.rank, self.world, self.epoch,
                                              self._err.data_ptr(), e.stream))
         return self.out
@@ -203,12 +216,11 @@ class TallyExchange:
         self.engine, self.torch = engine, torch
         self.rank, self.world = self.pair.rank, self.pair.world
         self.epoch = 0
-        self.out = torch.zeros(self.n + 1, dtype=torch.int64, device=engine.device)   # sums, then the status word
         r = _Reduce()
-        r.rank, r.world = self.rank, (self.world if self.pair.p2p else 1)
+        r.rank, r.world = (self.rank, self.world) if self.pair.p2p else (0, 1)
         if self.pair.p2p:
             r.peer_bufs_dev, r.peer_flags_dev = self.pair.hb.buffer_ptrs_dev, self.pair.hf.buffer_ptrs_dev
-        r.own_buf, r.n, r.out = self.pair.bufs.data_ptr(), self.n, self.out.data_ptr()
+        r.own_buf, r.n, r.out_offset = self.pair.bufs.data_ptr(), self.n, self.pair.out_offset
         self._r = r
 
     @property
@@ -241,17 +253,16 @@ class TallyExchange:
         pw.launch_kernel()
         if self.world == 1:
             return self.pair.half(h)
-        if self.pair.p2p:
-            return self.out[:self.n]
-        import torch.distributed as dist
-        self.out[:self.n].copy_(self.pair.half(h))
-        dist.all_reduce(self.out[:self.n], op=dist.ReduceOp.SUM)
-        self.out[self.n:].zero_()
-        return self.out[:self.n]
+        out = self.pair.sums()
+        if not self.pair.p2p:
+            import torch.distributed as dist
+            out.copy_(self.pair.half(h))
+            dist.all_reduce(out, op=dist.ReduceOp.SUM)
+        return out
 
     def status_view(self):
         """Device int64[1]: 0 after a good exchange, 1 when a peer did not arrive (copy it back with the result)."""
-        return self.out[self.n:]
+        return self.pair.status()
 
 
 def broadcast_array(arr, src: int = 0):

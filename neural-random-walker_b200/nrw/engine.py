@@ -48,7 +48,7 @@ class _Reduce(C.Structure):
                 ("peer_bufs_dev", C.c_void_p), ("peer_flags_dev", C.c_void_p),
                 ("own_buf", C.c_void_p),
                 ("offset", C.c_int64), ("zero_offset", C.c_int64), ("n", C.c_int64),
-                ("epoch", C.c_uint64), ("out", C.c_void_p)]
+                ("epoch", C.c_uint64), ("out_offset", C.c_int64)]
 
 
 class _Walk(C.Structure):
@@ -111,7 +111,7 @@ def load_library():
     lib.nrw_fluence_scores_host.argtypes = [vp, i32, i32, i32, vp, vp, i32, vp, vp, vp, i64, i64, u64,
                                             i32, C.POINTER(dbl * 4), vp, vp, C.POINTER(_Reduce), vp]
     lib.nrw_microbench.argtypes = [vp, i32, i32, i32, vp, vp, vp, vp]
-    lib.nrw_p2p_allreduce_i64.argtypes = [vp, vp, vp, vp, i64, i64, i64, i32, i32, u64, vp, vp]
+    lib.nrw_p2p_allreduce_i64.argtypes = [vp, vp, vp, i64, i64, i64, i64, i32, i32, u64, vp, vp]
     lib.nrw_guided_phases.argtypes = [i64, i64, i64, i64, i64, vp, vp, vp, C.POINTER(i32)]
     for name in EXPORTS:
         fn = getattr(lib, name)

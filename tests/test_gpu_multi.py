@@ -82,4 +82,6 @@ def test_fused_walk_exchange_two_ranks(p2p):
            "--master-addr", "127.0.0.1", "--master-port", str(29671 + int(p2p)), worker]
     env = dict(os.environ, NRW_P2P_REDUCE=p2p)
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=400, env=env)
+    if r.returncode != 0:
+        print(r.stderr[-8000:])
     assert r.returncode == 0 and "fused_exchange_worker ok p2p=%s" % (p2p == "1") in r.stdout, (r.stdout[-1500:], r.stderr[-3000:])
