@@ -6,5 +6,5 @@ NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
 $NVCC -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 \
       -Xcompiler -fPIC -Xcompiler -fvisibility=hidden -shared \
       ${NRW_NVCC_EXTRA:-} \
-      -o libnrw.so nrw_capi.cu -lcudart
-echo "built $(pwd)/libnrw.so"
+      -o ${NRW_LIB_OUT:-libnrw.so} nrw_capi.cu -lcudart
+echo "built $(pwd)/${NRW_LIB_OUT:-libnrw.so}"

@@ -17,7 +17,8 @@ from . import tables as _tables
 from .mesh import TransitionCSR
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "libnrw.so")
+# NRW_LIB: another build of the same library (A/B measurements of kernel changes); normally the in-tree one
+LIB_PATH = os.environ.get("NRW_LIB") or os.path.join(_HERE, "csrc", "libnrw.so")
 
 NRW_N_COUNTERS = 8
 COUNTER_NAMES = ("steps", "exits", "survivors", "t_overflow", "walkers")
