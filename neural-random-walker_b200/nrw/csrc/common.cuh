@@ -52,19 +52,29 @@ __host__ __device__ __forceinline__ uint32_t seed_to_key(uint64_t seed) {
     return (uint32_t)(z ^ (z >> 32));
 }
 
-// ---- COMPACT row descriptor word 0 (include/nrw.h): off[0:15) | n[15:25) | detcls[25:27) | detabs[27] |
-//      term[28] | detlast[29] | cls[30:32).  detabs marks a row whose single successor is absorbing; detcls
-//      is that successor's source class; detlast: that successor is the last row (the fluence sink);
-//      term = (n == 0) | detabs: a walker landing here ends in this iteration (tables.py::build_alias).
+// ---- COMPACT row descriptor (include/nrw.h).
+//   w0 = off[0:15) | n[15:25) | detabs[25] | term[26] | cls[27:29) | inc[29:32)
+//   w1 = base[0:29) | detlast[29] | sinc[30:32)
+// detabs marks a row whose single successor is absorbing; term = (n == 0) | detabs: a walker landing here ends in
+// this iteration; cls = source class of the row; detlast: the absorbing successor is the last row (the fluence
+// sink).  inc and sinc are what ARRIVING on the row adds to a walker's score and step count when rows with an
+// absorbing successor are stepped without a draw: inc = cls + (detabs ? class of the successor : 0),
+// sinc = 1 + detabs.  They sit in the top bits so that one shift-add each (LEA.HI) applies them, and so that a
+// base carrying its flag bits still addresses the right descriptor: (base + offset) << 3 drops bits 29..31
+// (tables.py::build_alias).
 constexpr uint32_t ROW_OFF_MASK = 0x00007fffu;
 constexpr uint32_t ROW_N_MASK   = 0x01ff8000u;
-constexpr uint32_t ROW_DETABS   = 0x08000000u;
-constexpr uint32_t ROW_TERM     = 0x10000000u;
-constexpr uint32_t ROW_DETLAST  = 0x20000000u;
+constexpr uint32_t ROW_DETABS   = 0x02000000u;
+constexpr uint32_t ROW_TERM     = 0x04000000u;
+constexpr uint32_t ROW_BASE_MASK = 0x1fffffffu;
+constexpr uint32_t ROW_DETLAST  = 0x20000000u;              // in w1
 __host__ __device__ __forceinline__ uint32_t row_off(uint32_t w0) { return w0 & ROW_OFF_MASK; }
 __host__ __device__ __forceinline__ uint32_t row_len(uint32_t w0) { return (w0 >> 15) & 0x3ffu; }
-__host__ __device__ __forceinline__ uint32_t row_detcls(uint32_t w0) { return (w0 >> 25) & 3u; }
-__host__ __device__ __forceinline__ uint32_t row_class(uint32_t w0) { return w0 >> 30; }
+__host__ __device__ __forceinline__ uint32_t row_class(uint32_t w0) { return (w0 >> 27) & 3u; }
+__host__ __device__ __forceinline__ uint32_t row_inc(uint32_t w0) { return w0 >> 29; }
+__host__ __device__ __forceinline__ uint32_t row_detcls(uint32_t w0) { return (w0 >> 29) - ((w0 >> 27) & 3u); }
+__host__ __device__ __forceinline__ uint32_t row_sinc(uint32_t w1) { return w1 >> 30; }
+__host__ __device__ __forceinline__ uint32_t row_base(uint32_t w1) { return w1 & ROW_BASE_MASK; }
 
 // numpy legacy random_sample(): (a >> 5, b >> 6) -> 53-bit double in [0, 1).
 __device__ __forceinline__ double u53(uint32_t a, uint32_t b) {
@@ -103,6 +113,13 @@ __device__ __forceinline__ uint32_t lanemask_lt() {
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
     return (uint32_t)__cvta_generic_to_shared(p);
+}
+// 8-byte shared-memory load from a 32-bit shared-window address (lets callers do the address arithmetic in 32
+// bits: an index whose top bits carry flags addresses the right entry once it is shifted left by 3)
+__device__ __forceinline__ uint2 lds64(uint32_t addr) {
+    uint2 v;
+    asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));
+    return v;
 }
 
 // ---- mbarrier + 1-D TMA bulk copy (global -> shared), SASS: UBLKCP ---------------------------

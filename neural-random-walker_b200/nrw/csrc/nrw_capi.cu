@@ -670,7 +670,7 @@ extern "C" int nrw_fluence_scores_host(nrw_engine* e, int32_t n_rows, int32_t n_
         // identity vector so that the walk takes the IDW kernel (walk_score.cuh)
         uint32_t present = 0;
         const uint32_t* ri = (const uint32_t*)rowinfo_host;
-        for (int32_t r = 0; r < n_rows; ++r) present |= 1u << (ri[2 * r] >> 30);
+        for (int32_t r = 0; r < n_rows; ++r) present |= 1u << row_class(ri[2 * r]);
         bool ident = true;
         for (uint32_t c = 0; c < 4; ++c) if ((present >> c) & 1u) ident = ident && class_value[c] == (double)c;
         for (int i = 0; i < 4; ++i) w.class_value[i] = ident ? (double)i : class_value[i];

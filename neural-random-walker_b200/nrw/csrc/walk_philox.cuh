@@ -86,8 +86,10 @@ __device__ __forceinline__ uint2 fac_row(const WalkParams& p, int k) {
     const uint32_t jn = j + d.y;                                   // target cell (wraps when negative)
     const uint32_t cls = (reinterpret_cast<const uint32_t*>(smem_fac + p.sm_fcls)[k >> 4] >> ((k & 15) * 2)) & 3u;
     const bool leaves = jn >= (uint32_t)p.fac_cells;
-    return make_uint2((leaves ? p.fac_exit_w0 : d.x) | (cls << 30),
-                      leaves ? p.fac_exit_base : jn * (uint32_t)p.fac_period);
+    // the class enters the cls field [27:29) and the inc field [29:32) (inc = cls + class of an absorbing successor,
+    // which the exit descriptor already carries): one multiply-add, no carry out of either field
+    return make_uint2((leaves ? p.fac_exit_w0 : d.x) + cls * 0x28000000u,
+                      leaves ? p.fac_exit_base : (jn * (uint32_t)p.fac_period) | 0x40000000u);
 }
 
 // Next id range [nb, nb + len) of a warp, or false when the launch's ids are exhausted (walk_score.cuh and the
@@ -142,15 +144,15 @@ struct RowRegs { uint32_t a, b, c, d; };   // COMPACT: a=w0 b=w1 | WIDE: off,n,b
 template <int TAB>
 __device__ __forceinline__ RowRegs<TAB> load_row(const WalkParams& p, const uint2* rowinfo_s, int k) {
     RowRegs<TAB> r;
-    if constexpr (TAB == TAB_SMEM) {
+    if constexpr (TAB == TAB_SMEM) {               // compact: b = the column base without its flag bits
         const uint2 v = rowinfo_s[k];
-        r.a = v.x; r.b = v.y; r.c = 0; r.d = 0;
+        r.a = v.x; r.b = row_base(v.y); r.c = 0; r.d = 0;
     } else if constexpr (TAB == TAB_HYB) {
         const uint2 v = __ldg(reinterpret_cast<const uint2*>(p.rowinfo) + k);
-        r.a = v.x; r.b = v.y; r.c = 0; r.d = 0;
+        r.a = v.x; r.b = row_base(v.y); r.c = 0; r.d = 0;
     } else if constexpr (TAB == TAB_FAC) {
         const uint2 v = fac_row(p, k);
-        r.a = v.x; r.b = v.y; r.c = 0; r.d = 0;
+        r.a = v.x; r.b = row_base(v.y); r.c = 0; r.d = 0;
     } else if constexpr (TAB == TAB_GLB) {
         const uint4 v = __ldg(reinterpret_cast<const uint4*>(p.rowinfo) + k);
         r.a = v.x; r.b = v.y; r.c = v.z; r.d = v.w;

@@ -15,10 +15,10 @@
 //   * the Philox round keys come from the kernel parameters (constant-bank operands), not from
 //     uniform-register arithmetic repeated every iteration;
 //   * the score is a per-lane running sum over the lane's walkers (flushed when the start node
-//     changes and at every range fetch), added to unconditionally each step; the step t = nt-1
-//     (outside the solution sum, fluence_mini_app.py:428) is dealt with on the rare path of walks
-//     ending within one step of the end of time; walker-steps are accumulated as lifetimes at death
-//     instead of once per step;
+//     changes and at every range fetch); the common step is branch-free: what arriving on a row adds to score
+//     and step count sits in the top bits of its descriptor (one shift-add each), no separate path for lanes
+//     whose walker ends; the step t = nt-1 (outside the solution sum, fluence_mini_app.py:428) is dealt with
+//     on the cold path of walkers within two steps of the end of time;
 //   * IDW: class weights equal to the class index need no weight lookup;
 //   * DET: a row whose single successor is absorbing (every exit row of the fluence mesh: 45 % of
 //     all walker-steps) is stepped without computing a draw -- slot 0 with threshold 2^32-1 is taken
@@ -33,11 +33,13 @@
 
 namespace nrw {
 
+// Descriptor of row k, where k may still carry the flag bits of the base it was formed from (bits 29..31 of w1:
+// common.cuh): in shared memory the 32-bit address arithmetic drops them ((k << 3) wraps), elsewhere they are masked.
 template <int TAB>
-__device__ __forceinline__ uint2 load_row2(const WalkParams& p, const uint2* rowinfo_s, int k) {
-    if constexpr (TAB == TAB_SMEM) return rowinfo_s[k];
-    else if constexpr (TAB == TAB_FAC) return fac_row(p, k);
-    else return __ldg(reinterpret_cast<const uint2*>(p.rowinfo) + k);
+__device__ __forceinline__ uint2 load_row2(const WalkParams& p, uint32_t rowinfo_a, uint32_t k) {
+    if constexpr (TAB == TAB_SMEM) return lds64(rowinfo_a + (k << 3));
+    else if constexpr (TAB == TAB_FAC) return fac_row(p, (int)(k & ROW_BASE_MASK));
+    else return __ldg(reinterpret_cast<const uint2*>(p.rowinfo) + (k & ROW_BASE_MASK));
 }
 
 // Philox2x32-10 with the ten round keys read from the kernel parameters (constant bank operands of
@@ -64,7 +66,7 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
     static_assert(tab_compact(TAB), "compact alias tables only");
     extern __shared__ __align__(16) unsigned char smem[];
     uint64_t* bar = reinterpret_cast<uint64_t*>(smem);
-    const uint2* rowinfo_s = reinterpret_cast<const uint2*>(smem + p.sm_rowinfo);
+    const uint32_t rowinfo_a = smem_u32(smem + p.sm_rowinfo);      // 32-bit shared-window address of the descriptors
     const uint2* alias_s = reinterpret_cast<const uint2*>(smem + p.sm_alias);
     uint32_t* hist_s = reinterpret_cast<uint32_t*>(smem + p.sm_hist);
     const int tid = threadIdx.x, lane = tid & 31;
@@ -109,8 +111,8 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
         if (k == sink_row) nsink += c;
         else atomicAdd(hist_s + k, c);
     };
-    auto det_target = [&](uint32_t w0, uint32_t base) -> int {   // the single successor of a detabs row
-        return (int)(base + (alias_s[row_off(w0)].y & 0xffffu));
+    auto det_target = [&](uint32_t w0, uint32_t w1) -> int {     // the single successor of a detabs row
+        return (int)(row_base(w1) + (alias_s[row_off(w0)].y & 0xffffu));
     };
     auto flush_score = [&]() {
         if (p.score && s >= 0 && x != 0)
@@ -155,7 +157,7 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
             s_lo = __ldg(p.start_prefix + s);
             s_end = __ldg(p.start_prefix + s + 1);
         }
-        srow = load_row2<TAB>(p, rowinfo_s, __ldg(p.start_nodes + s));
+        srow = load_row2<TAB>(p, rowinfo_a, (uint32_t)__ldg(p.start_nodes + s));
         sid_base = rbase + (p.start_id_base ? (__ldg(p.start_id_base + s) - s_lo) : 0ll);
         rebase();
         if (off >= s_end_off) pass_wrap();       // the new start's ids wrapped before this lane's first one
@@ -237,61 +239,53 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
         __syncwarp();
 
         // ---- one model step (fluence_mini_app.py:243-245 + the fused :428-434) -----------------------
+        // Cold: the walker is within two steps of the end of time (tn >= nt - 2).  Step nt - 1 is outside the
+        // solution sum (:428, Q3): it is taken and counted, not scored; a walker alive after it is a survivor.
+        auto near_end = [&](const uint2 row, const uint32_t knew, const int tn) {
+            const bool absorbed = (row.x & ROW_N_MASK) == 0u;
+            if (tn < t_last) {
+                x += weight_of(row_class(row.x));
+                if constexpr (HIST) tally_node((int)(knew & ROW_BASE_MASK), 1u);
+            }
+            ++nst;
+            t = tn;
+            if (absorbed) { t = -1; return; }
+            if (tn >= t_last) { ++nsurv; t = -1; return; }
+            if constexpr (DET) {
+                // tn == nt - 2 on a row whose single successor is absorbing: its exit step is step nt - 1 --
+                // a step and an exit, outside the sum
+                if (row.x & ROW_DETABS) { ++nst; t = -1; }
+            }
+        };
         auto step = [&](uint32_t slot, uint32_t coin) {
             const int tn = t + 1;
-            const uint32_t aoff = row_off(ra);
-            const uint2 e = alias_s[aoff + slot];
-            const int knew = (int)(rb + ((coin <= e.x) ? (e.y & 0xffffu) : (e.y >> 16)));
-            const uint2 row = load_row2<TAB>(p, rowinfo_s, knew);
+            const uint2 e = alias_s[row_off(ra) + slot];
+            // target row; rb still carries its flag bits, which the descriptor look-up drops (load_row2)
+            const uint32_t knew = rb + ((coin <= e.x) ? (e.y & 0xffffu) : (e.y >> 16));
+            const uint2 row = load_row2<TAB>(p, rowinfo_a, knew);
             ra = row.x; rb = row.y;
-            x += IDW ? (row.x >> 30) : ((p.cwpack >> ((row.x >> 27) & 0x18u)) & 0xffu);
-            t = tn;
-            // the walk ends here when the row is absorbing, when (DET) its single successor is, or at
-            // the last model step
-            const bool terminal = (row.x & (DET ? ROW_TERM : ROW_N_MASK)) == (DET ? ROW_TERM : 0u);
-            if (terminal || tn >= t_last) {
-                if (tn + 1 < t_last) [[likely]] {
-                    // an absorbing row, or (DET) a row whose single successor is absorbing (fluence exit
-                    // rows, fluence_mini_app.py:355-357): that step is taken now -- no draw could change it
-                    // (detcls is 0 on every row that is not such an exit row)
-                    if constexpr (HIST) {
-                        tally_node(knew, 1u);
-                        if constexpr (DET) {
-                            if (row.x & ROW_DETLAST) ++nsink;                         // the exit step, onto the sink
-                            else if (row.x & ROW_DETABS) [[unlikely]] tally_node(det_target(row.x, row.y), 1u);
-                        }
-                    }
-                    if constexpr (DET && IDW) {
-                        x += row_detcls(row.x);
-                        nst += (row.x >> 27) & 1u;
-                    } else if constexpr (DET) {
-                        if (row.x & ROW_DETABS) { x += weight_of(row_detcls(row.x)); ++nst; }
-                    }
-                    nst += (uint32_t)tn;
-                } else {
-                    // within one step of the end of time: step nt-1 is outside the sum (:428, Q3)
-                    int tl = tn;
-                    bool absorbed = (row.x & ROW_N_MASK) == 0u;
-                    uint32_t wl = weight_of(row_class(row.x));
-                    if constexpr (HIST) { if (tn < t_last) tally_node(knew, 1u); }
-                    if constexpr (DET) {
-                        if (!absorbed && tn < t_last) {
-                            wl = weight_of(row_detcls(row.x));
-                            x += wl;
-                            tl = tn + 1;              // == t_last: outside the sum, no histogram tally
-                            absorbed = true;
-                        }
-                    }
-                    if (tl >= t_last) {
-                        x -= wl;
-                        if (!absorbed) ++nsurv;
-                    }
-                    nst += (uint32_t)tl;
-                }
-                t = -1;
+            if (tn >= t_last - 1) [[unlikely]] { near_end(row, knew, tn); return; }
+            // Hot path, branch-free: this step and -- on a row whose single successor is absorbing (DET: the
+            // fluence exit rows, fluence_mini_app.py:355-357; no draw could change that step) -- the exit step it
+            // implies are both inside the sum; what they add to score and step count sits in the top bits of the
+            // descriptor (inc, sinc: common.cuh), one shift-add each.
+            if constexpr (IDW) {
+                x += DET ? row_inc(row.x) : row_class(row.x);
             } else {
-                if constexpr (HIST) atomicAdd(hist_s + knew, 1u);
+                x += weight_of(row_class(row.x));
+                if constexpr (DET) x += (row.x & ROW_DETABS) ? weight_of(row_detcls(row.x)) : 0u;
             }
+            nst += DET ? row_sinc(row.y) : 1u;
+            if constexpr (HIST) {
+                tally_node((int)(knew & ROW_BASE_MASK), 1u);
+                if constexpr (DET) {
+                    if (row.y & ROW_DETLAST) ++nsink;                         // the exit step, onto the sink
+                    else if (row.x & ROW_DETABS) [[unlikely]] tally_node(det_target(row.x, row.y), 1u);
+                }
+            }
+            // the walk ends here when the row is absorbing or (DET) its single successor is
+            const bool dead = (row.x & (DET ? ROW_TERM : ROW_N_MASK)) == (DET ? ROW_TERM : 0u);
+            t = dead ? -1 : tn;
         };
         // one Philox call serves the two steps of a pair (common.cuh, "paired draws"): lanes are refilled
         // only here, so every live lane is at an even t and the whole warp shares the call

@@ -28,7 +28,11 @@ from .mesh import TransitionCSR
 COMPACT_MAX_N = 1023
 COMPACT_MAX_REL = 65535
 COMPACT_MAX_ENTRIES = 1 << 15          # offsets are 15 bits: what one SM's shared memory can hold anyway
-ROW_N_SHIFT, ROW_DETCLS_SHIFT, ROW_DETABS_BIT, ROW_TERM_BIT, ROW_DETLAST_BIT, ROW_CLS_SHIFT = 15, 25, 27, 28, 29, 30
+# compact row descriptor (csrc/common.cuh): w0 = off[0:15) | n[15:25) | detabs[25] | term[26] | cls[27:29) | inc[29:32),
+# w1 = base[0:29) | detlast[29] | sinc[30:32)
+ROW_N_SHIFT, ROW_DETABS_BIT, ROW_TERM_BIT, ROW_CLS_SHIFT, ROW_INC_SHIFT = 15, 25, 26, 27, 29
+ROW_BASE_MASK, ROW_DETLAST_BIT, ROW_SINC_SHIFT = 0x1FFFFFFF, 29, 30
+ROW_CLASS_UNIT = (1 << ROW_CLS_SHIFT) + (1 << ROW_INC_SHIFT)      # what one unit of source class adds to w0
 
 
 def row_cum(csr: TransitionCSR) -> np.ndarray:
@@ -85,8 +89,8 @@ class FactoredRows:
     """Row descriptors of a translation-invariant mesh, factored so that they need no per-row table
     (walk_philox.cuh::fac_row): live row r = i + j * period (direction i, cell j) is
 
-    * a *stay* row when 0 <= j + shift[i] < cells: w0 = dir_w0[i] | class << 30, base = (j + shift[i]) * period
-    * an *exit* row otherwise:                      w0 = exit_w0   | class << 30, base = exit_base
+    * a *stay* row when 0 <= j + shift[i] < cells: w0 = dir_w0[i] + class * ROW_CLASS_UNIT, w1 = (j + shift[i]) * period | 1 << 30
+    * an *exit* row otherwise:                      w0 = exit_w0   + class * ROW_CLASS_UNIT, w1 = exit_base (with its flag bits)
 
     and rows >= n_live are kept verbatim in ``tail``.  ``cls_bits`` packs the 2-bit source classes of
     the live rows 16 to a word; ``k // period == (k * magic) >> shift`` for every k < n_live."""
@@ -109,8 +113,9 @@ class FactoredRows:
         out_of_mesh = (jn < 0) | (jn >= self.cells)
         kk = k.astype(np.int64)
         cls = (self.cls_bits[kk >> 4] >> ((kk & 15) * 2).astype(np.uint32)) & np.uint32(3)
-        w0 = np.where(out_of_mesh, np.uint32(self.exit_w0), self.dirtab[i, 0]) | (cls << np.uint32(30))
-        base = np.where(out_of_mesh, self.exit_base, jn * self.period)
+        w0 = (np.where(out_of_mesh, np.uint32(self.exit_w0), self.dirtab[i, 0]).astype(np.uint64)
+              + cls.astype(np.uint64) * np.uint64(ROW_CLASS_UNIT)) & np.uint64(0xFFFFFFFF)
+        base = np.where(out_of_mesh, self.exit_base, (jn * self.period) | (1 << ROW_SINC_SHIFT))
         return np.stack([w0.astype(np.uint32), base.astype(np.uint32)], axis=1)
 
 
@@ -127,8 +132,10 @@ def factorise_rows(at: "AliasTables", n_live: int):
     if n_live < 2 or not (1 <= n_tail <= 64):
         return None
     w0 = ri[:n_live, 0]
-    base = ri[:n_live, 1].astype(np.int64)
-    body = w0 & np.uint32(0x3FFFFFFF)
+    w1 = ri[:n_live, 1].astype(np.int64)
+    base = w1 & ROW_BASE_MASK
+    cls_all = (w0 >> np.uint32(ROW_CLS_SHIFT)) & np.uint32(3)
+    body = (w0.astype(np.int64) - cls_all.astype(np.int64) * ROW_CLASS_UNIT).astype(np.uint32)   # w0 without its class
     n = (w0 >> np.uint32(ROW_N_SHIFT)) & np.uint32(0x3FF)
     wide = n > 1
     if not wide.any():
@@ -152,11 +159,11 @@ def factorise_rows(at: "AliasTables", n_live: int):
     exit_w0 = exit_base = 0
     is_exit = np.zeros(n_live, dtype=bool)
     if narrow.any():
-        key = (body[narrow].astype(np.uint64) << np.uint64(32)) | base[narrow].astype(np.uint64)
+        key = (body[narrow].astype(np.uint64) << np.uint64(32)) | w1[narrow].astype(np.uint64)
         vals, cnts = np.unique(key, return_counts=True)
         top = int(vals[cnts.argmax()])
-        exit_w0, exit_base = top >> 32, top & 0xFFFFFFFF
-        is_exit = (body == np.uint32(exit_w0)) & (base == exit_base)
+        exit_w0, exit_base = top >> 32, top & 0xFFFFFFFF              # exit_base keeps its flag bits
+        is_exit = (body == np.uint32(exit_w0)) & (w1 == exit_base)
     stay = ~is_exit
     if (base[stay] % period).any():
         return None
@@ -172,7 +179,7 @@ def factorise_rows(at: "AliasTables", n_live: int):
     if np.abs(shifts).max() >= 1 << 30:
         return None
     dirtab[:, 1] = shifts.astype(np.int32).view(np.uint32)
-    cls = (w0 >> np.uint32(ROW_CLS_SHIFT)).astype(np.uint32)
+    cls = cls_all.astype(np.uint32)
     words = (n_live + 15) // 16
     padded = np.zeros(words * 16, dtype=np.uint32)
     padded[:n_live] = cls
@@ -293,12 +300,18 @@ def build_alias(csr: TransitionCSR, node_class: np.ndarray | None = None,
         detabs = (row_n == 1) & (row_n[first] == 0)
         detcls = np.where(detabs, node_class[first], 0).astype(np.uint32)
         detlast = detabs & (first == n - 1)                    # ... and it is the last row (the fluence sink)
-        w0 = (row_off | (row_n << np.uint32(ROW_N_SHIFT)) | (detcls << np.uint32(ROW_DETCLS_SHIFT))
+        if int(row_base.max(initial=0)) > ROW_BASE_MASK:
+            raise ValueError("compact layout: column bases must fit 29 bits")
+        # inc / sinc: what ARRIVING on the row adds to score and step count when rows with an absorbing successor
+        # are stepped without a draw (csrc/common.cuh): inc = cls + class of that successor, sinc = 1 + detabs
+        w0 = (row_off | (row_n << np.uint32(ROW_N_SHIFT))
               | (detabs.astype(np.uint32) << np.uint32(ROW_DETABS_BIT))
-              | (detlast.astype(np.uint32) << np.uint32(ROW_DETLAST_BIT))
               | ((detabs | (row_n == 0)).astype(np.uint32) << np.uint32(ROW_TERM_BIT))
-              | (node_class << np.uint32(ROW_CLS_SHIFT)))
-        rowinfo = np.stack([w0, row_base], axis=1).astype(np.uint32)
+              | (node_class << np.uint32(ROW_CLS_SHIFT))
+              | ((node_class + detcls) << np.uint32(ROW_INC_SHIFT)))
+        w1 = (row_base | (detlast.astype(np.uint32) << np.uint32(ROW_DETLAST_BIT))
+              | ((np.uint32(1) + detabs.astype(np.uint32)) << np.uint32(ROW_SINC_SHIFT)))
+        rowinfo = np.stack([w0, w1], axis=1).astype(np.uint32)
         ab = (a_all.astype(np.uint32) & np.uint32(0xFFFF)) | (b_all.astype(np.uint32) << np.uint32(16))
         alias = np.stack([th_all, ab], axis=1).astype(np.uint32)
         if alias.shape[0] == 0:
@@ -317,7 +330,7 @@ def build_alias(csr: TransitionCSR, node_class: np.ndarray | None = None,
 def alias_row_distribution(csr: TransitionCSR, at: AliasTables, row: int) -> dict:
     """Exact distribution the device draws from for ``row`` (for tests): {column: probability}."""
     if at.layout == "compact":
-        w0, base = int(at.rowinfo[row, 0]), int(at.rowinfo[row, 1])
+        w0, base = int(at.rowinfo[row, 0]), int(at.rowinfo[row, 1]) & ROW_BASE_MASK
         off, n = w0 & 0x7FFF, (w0 >> ROW_N_SHIFT) & 0x3FF
     else:
         off, n, base = (int(x) for x in at.rowinfo[row, :3])

@@ -49,8 +49,8 @@ def _decode_alias(at):
     if at.layout == "compact":
         off = (ri[:, 0] & 0x7FFF).astype(np.int64)
         n = ((ri[:, 0] >> 15) & 0x3FF).astype(np.int64)
-        cls = (ri[:, 0] >> 30).astype(np.int64)
-        base = ri[:, 1].astype(np.int64)
+        cls = ((ri[:, 0] >> 27) & 3).astype(np.int64)          # w0 = off | n << 15 | ... | cls << 27 | inc << 29
+        base = (ri[:, 1] & 0x1FFFFFFF).astype(np.int64)       # w1 = base | detlast << 29 | sinc << 30
         th = at.alias[:, 0].astype(np.uint32)
         a = (at.alias[:, 1] & 0xFFFF).astype(np.int64)
         b = (at.alias[:, 1] >> 16).astype(np.int64)

@@ -445,9 +445,11 @@ def test_deterministic_rows_on_a_general_graph(engine, k1_env):
     nc = (np.arange(n) % 4).astype(np.uint8)
     at = tables.build_alias(csr, node_class=nc)
     w0 = at.rowinfo[:, 0]
-    detabs = (w0 >> 27) & 1
+    detabs = (w0 >> 25) & 1
     assert detabs[5] == 1 and detabs[8] == 1 and detabs[6] == 0 and detabs[9] == 0 and detabs[10] == 0
-    assert ((w0[5] >> 25) & 3) == nc[55] and ((w0[8] >> 25) & 3) == nc[59]
+    cls, inc = (w0 >> 27) & 3, w0 >> 29                      # inc = cls + class of the absorbing successor
+    assert np.array_equal(cls, nc) and inc[5] - cls[5] == nc[55] and inc[8] - cls[8] == nc[59] and inc[6] == cls[6]
+    assert np.array_equal(at.rowinfo[:, 1] >> 30, 1 + detabs)  # sinc: steps an arrival accounts for
     tabs = engine.upload(csr, node_class=nc)
     starts = np.array([0, 5, 6, 7, 8, 9, 10, 3, 55, 21])
     counts = np.array([4000, 300, 300, 300, 77, 300, 50, 4000, 9, 2000])
