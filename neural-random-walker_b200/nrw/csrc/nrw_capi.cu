@@ -59,9 +59,7 @@ struct nrw_engine {
     // ring of ticket slots {work_next, done}: one per launch, handed back by the launch's last CTA (walk_tail.cuh)
     unsigned long long* slots;
     std::atomic<unsigned long long> next_slot;
-    std::mutex mu;                                            // attribute cache
     std::mutex mu_host;                                       // the *_host staging buffers (calls serialise)
-    std::unordered_map<const void*, int> smem_attr;           // kernel -> dynamic shared memory already opted in
     // grow-only staging buffers of nrw_fluence_scores_host
     void* d_rowinfo; size_t cap_rowinfo;
     void* d_alias; size_t cap_alias;
@@ -531,6 +529,18 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
 #undef Y
         }
     }
+    // time-resolved counts through the likely paths, nothing else tallied, compact tables: the trimmed walk too
+    if (tl == TL_CNT_G && p.cnt_path && tab_compact(tab) && w->nt >= 2 && !e->cfg.k1_general &&
+        32ll * (long long)w->nt < (1ll << 31)) {
+        while (p.range > 32 && p.range * (long long)w->nt >= (1ll << 31)) p.range = ((p.range / 2) / 32) * 32;
+#define Z(TAB)                                                                              \
+    if (tab == TAB) {                                                                       \
+        plan->fn = (const void*)walk_score_kernel<TAB, true, false, 1, false, true>;        \
+        plan->name = "walk_count<" #TAB ">";                                                \
+    }
+        Z(TAB_SMEM) Z(TAB_HYB) Z(TAB_FAC)
+#undef Z
+    }
     {   // guided range sizes (fetch_range, walk_philox.cuh).  NRW_RANGE_TAIL / NRW_TAIL_RANGES override
         // (0 ranges = one size)
         const long long warps = (long long)plan->grid * (plan->block / 32);
@@ -556,13 +566,18 @@ extern "C" int nrw_walk_philox_plan(nrw_engine* e, const nrw_tables* t, const nr
     return NRW_OK;
 }
 
-// opt a kernel in to `smem` bytes of dynamic shared memory once (the attribute call costs microseconds per launch)
+// Opt a kernel in to `smem` bytes of dynamic shared memory once (the attribute call costs microseconds per launch).
+// The attribute belongs to the function on a device, not to an engine: the cache is per (device, kernel), shared by
+// every engine of the process, and only ever raises the limit.
 static int ensure_smem(nrw_engine* e, const void* fn, int smem) {
-    std::lock_guard<std::mutex> lock(e->mu);
-    auto it = e->smem_attr.find(fn);
-    if (it != e->smem_attr.end() && it->second >= smem) return NRW_OK;
+    static std::mutex mu;
+    static std::unordered_map<unsigned long long, int> opted;          // (device, kernel) -> bytes opted in
+    const unsigned long long key = (unsigned long long)(uintptr_t)fn * 64ull + (unsigned long long)e->device;
+    std::lock_guard<std::mutex> lock(mu);
+    auto it = opted.find(key);
+    if (it != opted.end() && it->second >= smem) return NRW_OK;
     CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    e->smem_attr[fn] = smem;
+    opted[key] = smem;
     return NRW_OK;
 }
 

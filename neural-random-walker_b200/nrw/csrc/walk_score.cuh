@@ -60,10 +60,16 @@ __device__ __forceinline__ uint2 philox2x32_10_rk(uint32_t c0, uint32_t c1, cons
 // HIST: also tally every in-sum step at its target node (the occupancy histogram of walk_philox.cuh,
 // TL_HIST_S): shared-memory atomics for the nodes walkers spread over, a per-lane register count for
 // the one node they all end on (the last row: the sink), one merge into global memory per CTA.
-template <int TAB, bool IDW, bool DET, int CPS, bool HIST = false>
+// CNT: instead of a score, the time-resolved counts count_tn[t, node] (the reference's tempdata,
+// fluence_mini_app.py:227,245) in global memory, tallied through the likely path of every start
+// (nrw_walk.count_path, see walk_philox.cuh): a walker still on its start's path is not tallied step by step --
+// one shared-memory atomic records the step at which it leaves the path and the epilogue credits the path bins
+// from the suffix sums of that histogram; steps off the path go to their (diffuse) bins with plain REDs.
+template <int TAB, bool IDW, bool DET, int CPS, bool HIST = false, bool CNT = false>
 __global__ void __launch_bounds__(CPS == 1 ? 1024 : 768, CPS)
 walk_score_kernel(const __grid_constant__ WalkParams p) {
     static_assert(tab_compact(TAB), "compact alias tables only");
+    static_assert(!CNT || (!DET && !HIST), "the count walk draws every step and tallies nothing else");
     extern __shared__ __align__(16) unsigned char smem[];
     uint64_t* bar = reinterpret_cast<uint64_t*>(smem);
     const uint32_t rowinfo_a = smem_u32(smem + p.sm_rowinfo);      // 32-bit shared-window address of the descriptors
@@ -74,6 +80,12 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
                             reinterpret_cast<uint2*>(smem + p.sm_alias), tid);
     if constexpr (HIST)
         for (int i = tid; i < p.n_rows; i += (int)blockDim.x) hist_s[i] = 0u;
+    int32_t* path_s = reinterpret_cast<int32_t*>(smem + p.sm_path);
+    uint32_t* left_s = reinterpret_cast<uint32_t*>(smem + p.sm_left);
+    if constexpr (CNT) {
+        for (int i = tid; i < p.n_starts * p.t_cap; i += (int)blockDim.x) path_s[i] = __ldg(p.cnt_path + i);
+        for (int i = tid; i < p.n_starts * (p.t_cap + 1); i += (int)blockDim.x) left_s[i] = 0u;
+    }
     mbar_wait(bar, 0);
     __syncthreads();
     const int sink_row = p.n_rows - 1;           // HIST: the node every exit ends on is counted in registers
@@ -97,7 +109,8 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
     uint2 srow = make_uint2(0, 0);
     uint32_t x = 0;                              // score of the lane's walkers of start s since the last flush
                                                  // (flushed at a range fetch once it passes 2^31; planner bound: range * nt * weight < 2^31)
-    uint32_t nst = 0, nsurv = 0;                 // nst: < 2^32 between range fetches (range * nt bound)
+    uint32_t nst = 0, nsurv = 0, novf = 0;       // nst: < 2^32 between range fetches (range * nt bound)
+    bool onpath = false;                         // CNT: the lane's walker has followed its start's likely path so far
     unsigned long long nsteps = 0;
     // ---- warp-uniform id range [rbase + cur, rbase + end) ------------------------------------------
     long long rbase = 0;
@@ -183,6 +196,7 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
         c0 = c0_base + off;
         ra = srow.x; rb = srow.y;
         t = t_init;
+        if constexpr (CNT) onpath = true;
         if constexpr (DET) {
             x += det_w; nst += det_n;
             if constexpr (HIST) { nsink += det_hs; if (det_hn) [[unlikely]] atomicAdd(hist_s + det_tgt, 1u); }
@@ -258,6 +272,12 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
                 if (row.x & ROW_DETABS) { ++nst; t = -1; }
             }
         };
+        // CNT: leave event of a walker that was on its start's path until step l - 1 (l = first step off the path,
+        // the step after its last one, or t_cap)
+        auto leave_path = [&](int l) {
+            atomicAdd(left_s + s * (p.t_cap + 1) + min(l, p.t_cap), 1u);
+            onpath = false;
+        };
         auto step = [&](uint32_t slot, uint32_t coin) {
             const int tn = t + 1;
             const uint2 e = alias_s[row_off(ra) + slot];
@@ -265,6 +285,30 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
             const uint32_t knew = rb + ((coin <= e.x) ? (e.y & 0xffffu) : (e.y >> 16));
             const uint2 row = load_row2<TAB>(p, rowinfo_a, knew);
             ra = row.x; rb = row.y;
+            if constexpr (CNT) {
+                const int k = (int)(knew & ROW_BASE_MASK);
+                if (tn < p.t_cap) {
+                    if (!(onpath && k == path_s[s * p.t_cap + tn])) {      // on the path: credited in the epilogue
+                        if (onpath) leave_path(tn);
+                        const long long gq = p.per_start ? s : 0;
+                        atomicAdd(p.count_tn + (gq * p.t_cap + tn) * (long long)p.n_rows + k, 1u);
+                    }
+                } else {
+                    ++novf;
+                    if (onpath) leave_path(p.t_cap);
+                }
+                // every step is counted as it is taken; the walk ends on an absorbing row or after step nt - 1
+                ++nst;
+                const bool absorbed = (row.x & ROW_N_MASK) == 0u;
+                if (absorbed || tn >= t_last) {
+                    if (!absorbed) ++nsurv;
+                    if (onpath) leave_path(tn + 1);
+                    t = -1;
+                } else {
+                    t = tn;
+                }
+                return;
+            }
             if (tn >= t_last - 1) [[unlikely]] { near_end(row, knew, tn); return; }
             // Hot path, branch-free: this step and -- on a row whose single successor is absorbing (DET: the
             // fluence exit rows, fluence_mini_app.py:355-357; no draw could change that step) -- the exit step it
@@ -315,6 +359,24 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
         if (wwalk - v2) atomicAdd(p.counters + 1, wwalk - v2);          // exits = walkers - survivors
         if (v2) atomicAdd(p.counters + 2, (unsigned long long)v2);
         if (wwalk) atomicAdd(p.counters + 4, wwalk);
+    }
+    if constexpr (CNT) {
+        uint32_t v3 = novf;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v3 += __shfl_xor_sync(NRW_FULL_MASK, v3, o);
+        if (lane == 0 && p.counters && v3) atomicAdd(p.counters + 3, (unsigned long long)v3);
+        // walkers on the path at step tau = those that left it later: suffix sums of the leave-time histogram
+        __syncthreads();
+        for (int sidx = tid; sidx < p.n_starts; sidx += (int)blockDim.x) {
+            const long long gq = p.per_start ? sidx : 0;
+            unsigned long long on = left_s[sidx * (p.t_cap + 1) + p.t_cap];
+            for (int tau = p.t_cap - 1; tau >= 1; --tau) {
+                const int node = path_s[sidx * p.t_cap + tau];
+                if (on && node >= 0)
+                    atomicAdd(p.count_tn + (gq * p.t_cap + tau) * (long long)p.n_rows + node, (uint32_t)on);
+                on += left_s[sidx * (p.t_cap + 1) + tau];
+            }
+        }
     }
     if constexpr (HIST) {
 #pragma unroll

@@ -20,10 +20,11 @@ def _ref_counts(port):
 
 
 @pytest.mark.parametrize("per_start", [False, True])
-def test_likely_path_tally_equals_the_plain_tally(engine, c1_csr, per_start):
+def test_likely_path_tally_equals_the_plain_tally(engine, c1_csr, per_start, monkeypatch):
     """Global time-resolved counts with and without the leave-time histogram, against the numpy port: ragged starts
     (an empty one, the sink itself, a repeated node), a window shorter than the walk (t_cap < nt: overflow), and
-    a window longer than any walk."""
+    a window longer than any walk.  With the path the trimmed count walk runs (walk_score.cuh, CNT), under
+    NRW_K1=general the general kernel's path tally, without a path the general kernel's hot-bin cache."""
     from oracle import philox_port
     tabs = engine.upload(c1_csr)
     starts = np.array([435, 0, 900, 14, 14, 899, 450, 464])
@@ -31,17 +32,21 @@ def test_likely_path_tally_equals_the_plain_tally(engine, c1_csr, per_start):
     for nt, t_cap in ((64, 64), (64, 40), (300, 300)):
         port = philox_port.walk_port(c1_csr, starts, counts, nt, 9, alias=tabs.alias_host, t_cap=t_cap,
                                      count_per_start=per_start)
-        got = {}
-        for path in (True, False):
+        for path, general, want in ((True, False, "walk_count<"), (True, True, "32>"), (False, False, "32>")):
+            if general:
+                monkeypatch.setenv("NRW_K1", "general")
+            else:
+                monkeypatch.delenv("NRW_K1", raising=False)
             res = engine.walk(tabs, starts, counts, nt, 9, count_tn=True, t_cap=t_cap, count_per_start=per_start,
                               count_path=path)
-            assert "32>" in res.kernel, res.kernel          # TL_CNT_G: the bins do not fit shared memory
-            got[path] = _counts(res)
+            assert want in res.kernel, res.kernel           # "32>": TL_CNT_G, the bins do not fit shared memory
             c = res.counters_dict()
             for k in ("steps", "exits", "survivors", "walkers"):
-                assert c[k] == port["counters"][k], (k, path)
-        assert np.array_equal(got[True], _ref_counts(port)), (nt, t_cap)
-        assert np.array_equal(got[False], _ref_counts(port)), (nt, t_cap)
+                assert c[k] == port["counters"][k], (k, path, general)
+            if t_cap < nt:
+                assert c["t_overflow"] > 0
+            assert np.array_equal(_counts(res), _ref_counts(port)), (nt, t_cap, path, general)
+        monkeypatch.delenv("NRW_K1", raising=False)
 
 
 def test_likely_path_tally_on_a_general_graph(engine):
