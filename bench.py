@@ -529,6 +529,11 @@ def roofline_object(eng, csr, steps_from, kernel, kernel_ms, steps_per_launch, d
     if facts and (facts.get("kernel") != kernel or int(facts.get("walker_steps_per_launch", -1)) != steps_per_launch):
         stale = ("stale capture: %s with %s walker-steps per launch, this run: %s with %d"
                  % (facts.get("kernel"), facts.get("walker_steps_per_launch"), kernel, steps_per_launch))
+    if facts and not stale:
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        from ncu_summary import csrc_sha256
+        if facts.get("csrc_sha256") != csrc_sha256():
+            stale = "stale capture: the CUDA sources changed since it was taken (csrc_sha256 differs)"
     sm_mhz = clocks.get("sm_mhz") or clocks.get("sm_max_mhz") or 1965.0
     peak = eng.n_sms * 4 * sm_mhz * 1e6                       # warp-instructions / s the schedulers can issue
     peak_hbm, peak_src = measured_peak()

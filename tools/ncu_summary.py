@@ -44,15 +44,31 @@ def plan_name(ncu_name):
     """ncu's demangled kernel name -> the planner's name (nrw_walk_philox_plan), e.g.
     walk_score_kernel<0, 1, 1, 1, 0> -> walk_score<TAB_SMEM,true,true,cps=1>."""
     import re
-    m = re.search(r"walk_score_kernel<\(?(?:int\))?(\d+), \(?(?:bool\))?(\d+), \(?(?:bool\))?(\d+), \(?(?:int\))?(\d+), \(?(?:bool\))?(\d+)>", ncu_name)
+    m = re.search(r"walk_score_kernel<([^>]*)>", ncu_name)
     if m:
-        tab, idw, det, cps, hist = (int(x) for x in m.groups())
+        args = [int(x) for x in re.findall(r"\d+", re.sub(r"\((?:int|bool)\)", "", m.group(1)))]
+        tab, idw, det, cps, hist = args[:5]
+        if len(args) > 5 and args[5]:
+            return "walk_count<%s>" % TAB_NAMES[tab]
         return "%s<%s,%s,%s,cps=%d>" % ("walk_score_hist" if hist else "walk_score", TAB_NAMES[tab],
                                         "true" if idw else "false", "true" if det else "false", cps)
     m = re.search(r"walk_philox_kernel<\(?(?:int\))?(\d+), \(?(?:int\))?(\d+)>", ncu_name)
     if m:
         return "walk_philox<%s,%d>" % (TAB_NAMES[int(m.group(1))], int(m.group(2)))
     return ncu_name
+
+
+def csrc_sha256():
+    """Digest of the CUDA sources the library is built from: bench.py refuses a capture of other kernel code."""
+    import glob
+    import hashlib
+    import os
+    root = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "neural-random-walker_b200", "nrw", "csrc")
+    h = hashlib.sha256()
+    for f in sorted(glob.glob(os.path.join(root, "*.cu")) + glob.glob(os.path.join(root, "*.cuh"))):
+        h.update(os.path.basename(f).encode())
+        h.update(open(f, "rb").read())
+    return h.hexdigest()
 
 
 def traffic_json(h, data, out_path, argv):
@@ -66,7 +82,7 @@ def traffic_json(h, data, out_path, argv):
     units = argv["units"]
     facts = {"kernel": plan_name(r[h.index("Kernel Name")]),
              "dram_bytes_per_launch": (bytes_of("dram__bytes_read.sum", units) or 0.0) + (bytes_of("dram__bytes_write.sum", units) or 0.0),
-             "round": argv.get("round"), "source": argv.get("source"),
+             "round": argv.get("round"), "source": argv.get("source"), "csrc_sha256": csrc_sha256(),
              "ncu_kernel_us": (val("gpu__time_duration.sum") or 0.0) * {"ns": 1e-3, "us": 1.0, "ms": 1e3, "s": 1e6}.get(
                  units[h.index("gpu__time_duration.sum")], 1.0),
              "warp_inst_per_launch": val("smsp__inst_executed.sum"),
