@@ -58,11 +58,17 @@ typedef struct nrw_engine nrw_engine;   /* opaque handle: one per (process, devi
 #define NRW_ALIAS_COMPACT 1   /* rowinfo 8 B/row, alias 8 B/entry, <= 2^15 entries (shared memory) */
 #define NRW_ALIAS_WIDE    2   /* rowinfo 16 B/row, alias 16 B/entry (any graph, global)  */
 
-/* COMPACT rowinfo  (uint32 w0, w1):  w0 = off[0:15) | n[15:25) | detcls[25:27) | detabs[27] | term[28] | detlast[29] | cls[30:32),
- *                  w1 = base.  detabs = 1: the row has ONE successor and it is absorbing (an exit row
- *                  of fluence_mini_app.py:355-357); detcls = source class of that successor;
- *                  detlast = 1: that successor is row n_rows - 1;  term = (n == 0) | detabs.  The
- *                  score kernel steps such rows without a draw (the draw cannot change the outcome).
+/* COMPACT rowinfo  (uint32 w0, w1):
+ *                  w0 = off[0:15) | n[15:25) | detabs[25] | term[26] | cls[27:29) | inc[29:32)
+ *                  w1 = base[0:29) | detlast[29] | sinc[30:32)
+ *                  detabs = 1: the row has ONE successor and it is absorbing (an exit row of
+ *                  fluence_mini_app.py:355-357); detlast = 1: that successor is row n_rows - 1;
+ *                  term = (n == 0) | detabs; cls = source class of the row.  The score kernel steps detabs
+ *                  rows without a draw (the draw cannot change the outcome), and inc / sinc are what
+ *                  ARRIVING on the row then adds to a walker's score and step count:
+ *                  inc = cls + (detabs ? class of the successor : 0), sinc = 1 + detabs.  They sit in the
+ *                  top bits so that one shift-add each applies them and so that base + offset, flags
+ *                  included, still addresses the right descriptor in shared memory ((k << 3) drops them).
  *         alias    (uint32 thresh, ab): target = base + ((coin <= thresh) ? ab & 0xffff : ab >> 16),
  *                  slot and coin = high and low word of w * n, w = one 32-bit Philox word (csrc/common.cuh)
  * WIDE    rowinfo  (uint32 off, n, base, cls)
