@@ -298,6 +298,34 @@ NRW_API int  nrw_fluence_scores_host(nrw_engine* e,
                              int64_t* score_host, unsigned long long* counters_host,
                              const nrw_reduce* reduce, void* stream);
 
+/* nrw_fluence_scores_host WITHOUT any allocation, for callers that cannot call cudaMalloc (code under CUDA
+ * graph capture, tight serving loops, harnesses that forbid it).  Same arguments and results as
+ * nrw_fluence_scores_host with reduce == NULL (one GPU), bit for bit; but every device-side buffer the call needs
+ * -- the staged copies of the tables and of the start list, the tally (scores + counters) and the launch's ticket
+ * slot -- lives in ONE file-scope `static __device__` array of NRW_STATIC_SCRATCH_BYTES (1 MiB) inside libnrw.so
+ * instead of cudaMalloc'ed buffers that grow on demand.  Every GPU that loads the library holds that array until
+ * the process exits.  The call (and nothing it calls) uses cudaMalloc, cudaFree or any allocating routine; the
+ * array's device address is resolved once per device with cudaGetSymbolAddress on the first call for that device.
+ * Limit: 256 (ticket slot) + the 256-byte-rounded sizes of (n_starts + 8) * 8 [tally], n_rows * 8 [row
+ * descriptors], n_alias * 8 [alias entries], n_starts * 4, (n_starts + 1) * 8 and (with start_id_base_host)
+ * n_starts * 8 bytes must fit NRW_STATIC_SCRATCH_BYTES -- the 10 001-row C5 mesh with all 10 000 starts needs
+ * 0.42 MiB; larger problems are refused with NRW_ENOSPC and a message that names both numbers.
+ * ALL calls of a process on one device share the array, which keeps the previous call's contents: the call
+ * clears what must start at zero (tally, ticket slot) itself, and two calls that overlap on the GPU (two streams,
+ * two threads) would race on it -- the library serialises callers behind a mutex and returns only after `stream`
+ * has been synchronised, so calls through this entry never overlap; do not use the array in any other way.
+ * No counterpart in the reference. */
+#define NRW_STATIC_SCRATCH_BYTES (1 << 20)
+NRW_API int  nrw_fluence_scores_host_static(nrw_engine* e,
+                             int32_t n_rows, int32_t n_live, int32_t n_alias,
+                             const void* rowinfo_host, const void* alias_host,
+                             int32_t n_starts, const int32_t* start_nodes_host,
+                             const int64_t* start_prefix_host, const int64_t* start_id_base_host,
+                             int64_t walker_lo, int64_t walker_hi, uint64_t seed, int32_t nt,
+                             const double class_value[4],
+                             int64_t* score_host, unsigned long long* counters_host,
+                             void* stream);
+
 /* The path's one collective over peer memory (no NCCL) as a stand-alone launch: afterwards
  * peer_bufs[q][out_offset + i] = sum over ranks r of peer_bufs[r][offset + i] on every rank q (i < n).  Same
  * protocol, buffer layout and alternation rule as nrw_reduce above (the walk runs this exchange in its own tail;

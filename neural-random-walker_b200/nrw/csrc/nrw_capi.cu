@@ -709,6 +709,108 @@ extern "C" int nrw_fluence_scores_host(nrw_engine* e, int32_t n_rows, int32_t n_
     return NRW_OK;
 }
 
+// ---- the host-buffer entry without any allocation (no counterpart in the reference; operators' request) -------
+// ALL device-side buffers of the call live in this file-scope array: every GPU that loads the library holds its
+// 1 MiB until the process exits.  In HOST code the name `g_static_scratch` is a host-side stand-in, not a device
+// address: the address a kernel or a copy may use comes from cudaGetSymbolAddress, resolved once per device with
+// that device current (static_scratch_base).  Calls share the array and it keeps the last call's contents.
+static __device__ __align__(256) unsigned char g_static_scratch[NRW_STATIC_SCRATCH_BYTES];
+
+static std::mutex g_static_mu;                               // one caller at a time: the array is shared
+static unsigned char* g_static_base[64] = {nullptr};         // device address of g_static_scratch per device
+
+// Device address of the static scratch on `device` (which the caller has made current); resolved once per device.
+static int static_scratch_base(int device, unsigned char** base) {
+    if (device < 0 || device >= 64) return fail(NRW_EINVAL, "nrw_fluence_scores_host_static: device %d", device);
+    if (!g_static_base[device]) {
+        void* ptr = nullptr;
+        CUDA_TRY(cudaGetSymbolAddress(&ptr, g_static_scratch));
+        if (!ptr) return fail(NRW_ECUDA, "nrw_fluence_scores_host_static: cudaGetSymbolAddress returned NULL");
+        g_static_base[device] = (unsigned char*)ptr;
+    }
+    *base = g_static_base[device];
+    return NRW_OK;
+}
+
+extern "C" int nrw_fluence_scores_host_static(nrw_engine* e, int32_t n_rows, int32_t n_live, int32_t n_alias,
+                                              const void* rowinfo_host, const void* alias_host,
+                                              int32_t n_starts, const int32_t* start_nodes_host,
+                                              const int64_t* start_prefix_host, const int64_t* start_id_base_host,
+                                              int64_t walker_lo, int64_t walker_hi, uint64_t seed, int32_t nt,
+                                              const double class_value[4], int64_t* score_host,
+                                              unsigned long long* counters_host, void* stream) {
+    if (!e || !rowinfo_host || !alias_host || !start_nodes_host || !start_prefix_host || !score_host ||
+        !class_value || n_rows <= 0 || n_alias <= 0 || n_starts <= 0)
+        return fail(NRW_EINVAL, "nrw_fluence_scores_host_static: bad argument");
+    // carve-up of the static array (256-byte aligned pieces); sizes beyond it are refused before anything is touched
+    auto up256 = [](size_t b) { return (b + 255) & ~(size_t)255; };
+    const size_t n_tally = (size_t)n_starts + NRW_N_COUNTERS;
+    const size_t o_slot = 0;
+    const size_t o_tally = o_slot + 256;
+    const size_t o_row = o_tally + up256(n_tally * 8);
+    const size_t o_alias = o_row + up256((size_t)n_rows * 8);
+    const size_t o_starts = o_alias + up256((size_t)n_alias * 8);
+    const size_t o_prefix = o_starts + up256((size_t)n_starts * 4);
+    const size_t o_idbase = o_prefix + up256(((size_t)n_starts + 1) * 8);
+    const size_t need = o_idbase + (start_id_base_host ? up256((size_t)n_starts * 8) : 0);
+    if (need > (size_t)NRW_STATIC_SCRATCH_BYTES)
+        return fail(NRW_ENOSPC, "nrw_fluence_scores_host_static: n_rows=%d n_alias=%d n_starts=%d need %zu bytes of scratch, "
+                    "the static array holds %d (use nrw_fluence_scores_host)", n_rows, n_alias, n_starts, need,
+                    (int)NRW_STATIC_SCRATCH_BYTES);
+    cudaStream_t st = (cudaStream_t)stream;
+    std::lock_guard<std::mutex> lock(g_static_mu);
+    CUDA_TRY(cudaSetDevice(e->device));
+    unsigned char* base = nullptr;
+    int rc;
+    if ((rc = static_scratch_base(e->device, &base))) return rc;
+    unsigned long long* slot = (unsigned long long*)(base + o_slot);
+    long long* tally = (long long*)(base + o_tally);
+    // the array keeps the previous call's contents: ticket slot and tally must start at zero
+    CUDA_TRY(cudaMemsetAsync(base + o_slot, 0, o_row, st));
+    CUDA_TRY(cudaMemcpyAsync(base + o_row, rowinfo_host, (size_t)n_rows * 8, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(base + o_alias, alias_host, (size_t)n_alias * 8, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(base + o_starts, start_nodes_host, (size_t)n_starts * 4, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(base + o_prefix, start_prefix_host, ((size_t)n_starts + 1) * 8, cudaMemcpyHostToDevice, st));
+    if (start_id_base_host)
+        CUDA_TRY(cudaMemcpyAsync(base + o_idbase, start_id_base_host, (size_t)n_starts * 8, cudaMemcpyHostToDevice, st));
+    nrw_tables t;
+    memset(&t, 0, sizeof(t));
+    t.n_rows = n_rows; t.n_live = n_live; t.alias_layout = NRW_ALIAS_COMPACT; t.n_alias = n_alias;
+    t.rowinfo = base + o_row; t.alias = base + o_alias;
+    nrw_walk w;
+    memset(&w, 0, sizeof(w));
+    w.n_starts = n_starts; w.start_nodes = (const int32_t*)(base + o_starts);
+    w.start_prefix = (const int64_t*)(base + o_prefix);
+    w.start_id_base = start_id_base_host ? (const int64_t*)(base + o_idbase) : nullptr;
+    w.walker_lo = walker_lo; w.walker_hi = walker_hi; w.seed = seed; w.nt = nt;
+    w.sampler = NRW_SAMPLER_ALIAS; w.score = (int64_t*)tally;
+    {   // as in nrw_fluence_scores_host: identity weights on the classes in use select the IDW kernel
+        uint32_t present = 0;
+        const uint32_t* ri = (const uint32_t*)rowinfo_host;
+        for (int32_t r = 0; r < n_rows; ++r) present |= 1u << row_class(ri[2 * r]);
+        bool ident = true;
+        for (uint32_t c = 0; c < 4; ++c) if ((present >> c) & 1u) ident = ident && class_value[c] == (double)c;
+        for (int i = 0; i < 4; ++i) w.class_value[i] = ident ? (double)i : class_value[i];
+    }
+    w.counters = (unsigned long long*)(tally + n_starts);
+    // plan + launch as nrw_walk_philox does, with the ticket slot in the static array instead of the engine's ring
+    WalkPlan plan;
+    if ((rc = make_plan(e, &t, &w, &plan))) return rc;
+    if (w.walker_hi > w.walker_lo) {
+        if ((rc = ensure_smem(e, plan.fn, plan.smem))) return rc;
+        plan.p.work_next = slot;
+        plan.p.tail.slot = slot;
+        void* args[] = {&plan.p};
+        CUDA_TRY(cudaLaunchKernel(plan.fn, dim3(plan.grid), dim3(plan.block), args, plan.smem, st));
+    }
+    CUDA_TRY(cudaMemcpyAsync(score_host, tally, (size_t)n_starts * 8, cudaMemcpyDeviceToHost, st));
+    if (counters_host)
+        CUDA_TRY(cudaMemcpyAsync(counters_host, tally + n_starts, NRW_N_COUNTERS * sizeof(unsigned long long),
+                                 cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    return NRW_OK;
+}
+
 // ---- the path's collective over peer memory ------------------------------------------------------
 extern "C" int nrw_p2p_allreduce_i64(nrw_engine* e, const void* peer_bufs_dev, const void* peer_flags_dev,
                                      int64_t offset, int64_t zero_offset, int64_t out_offset, int64_t n,
