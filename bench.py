@@ -526,7 +526,11 @@ def roofline_object(eng, csr, steps_from, kernel, kernel_ms, steps_per_launch, d
             stale = "unreadable: %s" % exc
     else:
         stale = "profiles/walk_traffic.json missing"
-    if facts and (facts.get("kernel") != kernel or int(facts.get("walker_steps_per_launch", -1)) != steps_per_launch):
+    # same kernel and the same workload: the walker-steps of the captured launch, or -- on a rank of an N > 1 job, which
+    # walks another slice of the stream ids of the same workload -- within 0.1 % of it (the instruction count is then
+    # scaled by the ratio of the walker-steps and the line says so)
+    cap_steps = int(facts.get("walker_steps_per_launch", -1)) if facts else -1
+    if facts and (facts.get("kernel") != kernel or abs(cap_steps - steps_per_launch) > 1e-3 * steps_per_launch):
         stale = ("stale capture: %s with %s walker-steps per launch, this run: %s with %d"
                  % (facts.get("kernel"), facts.get("walker_steps_per_launch"), kernel, steps_per_launch))
     if facts and not stale:
@@ -547,7 +551,9 @@ def roofline_object(eng, csr, steps_from, kernel, kernel_ms, steps_per_launch, d
         r.update(achieved=None, frac=None, traffic=None, stale=stale)
         dram = None
     else:
-        wi = float(facts["warp_inst_per_launch"])
+        wi = float(facts["warp_inst_per_launch"]) * steps_per_launch / cap_steps
+        if cap_steps != steps_per_launch:
+            r["instruction_count_scaled_from_capture_by"] = steps_per_launch / cap_steps
         dram = facts.get("dram_bytes_per_launch")
         drawn = steps_per_launch * (1.0 - det_frac)
         r.update(achieved=wi / (kernel_ms * 1e-3), frac=wi / (kernel_ms * 1e-3) / peak, traffic=dram,

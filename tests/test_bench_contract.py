@@ -18,8 +18,8 @@ def _last_line(path):
 
 def test_committed_gpu_lines_carry_the_contract_keys():
     """Round-2 lines: N = 1 (full, with the side legs), N = 2 and N = 8 (the walk's fused exchange)."""
-    paths = [os.path.join(ROOT, "profiles", n) for n in ("r02v_bench_n1_full.json", "r02r_bench_n2.json",
-                                                         "r02s_bench_n8.json")]
+    paths = [os.path.join(ROOT, "profiles", n) for n in ("r02v_bench_n1_full.json", "r02w_bench_n2.json",
+                                                         "r02w_bench_n8.json")]
     for path in paths:
         d = _last_line(path)
         for k in BASE_KEYS + ("roofline", "e2e", "gpu_launches", "clocks", "ms_p50", "ms_p95", "fluence_err",
