@@ -23,7 +23,7 @@
  *     be in flight at once).  The *_host entries stage through per-engine buffers and serialise
  *     behind a per-engine mutex;
  *   - environment: the measurement switches (NRW_K1, NRW_DET, NRW_TAB, NRW_CPS, NRW_RANGES_PER_WARP,
- *     NRW_RANGE_TAIL, NRW_TAIL_RANGES, NRW_CNT_MATCH, NRW_CNT_CACHE, NRW_CNT_PATH)
+ *     NRW_RANGE_TAIL, NRW_TAIL_RANGES, NRW_CNT_MATCH, NRW_CNT_CACHE, NRW_CNT_PATH, NRW_STR)
  *     are read ONCE, in nrw_create, and stored in the handle (nrw_engine_config prints them); no
  *     launch calls getenv.  None of them changes a result.
  */
@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define NRW_ABI_VERSION 3
+#define NRW_ABI_VERSION 4
 
 #if defined(__GNUC__)
 #define NRW_API __attribute__((visibility("default")))
@@ -113,6 +113,20 @@ typedef struct nrw_tables {
      * uniform per level: left iff u7 < threshold.  NULL when absent.                                    */
     const uint8_t* tree;      /* [tree_ptr[n_rows]]                                        */
     const int32_t* tree_ptr;  /* [n_rows + 1]; row r owns n2(r) - 1 entries (0 for n <= 1) */
+    /* Optional, COMPACT layout only: the STRUCTURED form of the same tables, for matrices whose alias tables have
+     * the closed form of the fluence matrix (fluence_mini_app.py:368-371: keep the direction with probability
+     * 1 - pone, else scatter uniformly): every alias entry s of a row is (str_thresh, own = s, alias = same), one
+     * threshold for the whole matrix, so that  target = base + (coin <= str_thresh ? slot : same)  needs no alias
+     * look-up.  rowinfo_str = rowinfo with `same` in place of the pattern offset (w0 bits [0:15));
+     * nrw/tables.py::structure_rows builds it and verifies every entry, so the structured draw yields the alias
+     * draw's target for every (slot, coin).  The score walk takes it when present (one shared-memory look-up per
+     * step instead of two, no alias patterns staged).  fac_*_str: the factored form of rowinfo_str (period, cells,
+     * shift, magic, class bits and exit base are those of fac_*).  All NULL / 0 when absent.            */
+    const void* rowinfo_str;  /* [n_rows] uint32 (w0, w1)                                   */
+    uint32_t str_thresh;
+    uint32_t fac_exit_w0_str;
+    const void* fac_dir_str;  /* uint32 [fac_period][2]                                     */
+    const void* fac_tail_str; /* uint32 [fac_n_tail][2]                                     */
 } nrw_tables;
 
 /* ---- Philox walk (K1) -------------------------------------------------------------- */

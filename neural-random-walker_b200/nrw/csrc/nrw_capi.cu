@@ -49,6 +49,7 @@ struct nrw_config {
     int cnt_match;         // NRW_CNT_MATCH: -1 auto, 0 plain, 1 match_any aggregation
     int cnt_cache;         // NRW_CNT_CACHE=0: no CTA-level cache of hot bins
     int cnt_path;          // NRW_CNT_PATH=0: ignore nrw_walk.count_path
+    int str;               // NRW_STR=0: ignore nrw_tables.rowinfo_str (alias look-ups in the score walk)
 };
 
 struct nrw_engine {
@@ -88,6 +89,7 @@ static nrw_config config_from_env() {
     c.cnt_match = getenv("NRW_CNT_MATCH") ? (env_int("NRW_CNT_MATCH", 1) != 0) : -1;
     c.cnt_cache = env_int("NRW_CNT_CACHE", 1) != 0;
     c.cnt_path = env_int("NRW_CNT_PATH", 1) != 0;
+    c.str = env_int("NRW_STR", 1) != 0;
     return c;
 }
 
@@ -141,9 +143,9 @@ extern "C" int nrw_engine_config(nrw_engine* e, char* buf, int buf_len) {
     const nrw_config& c = e->cfg;
     snprintf(buf, (size_t)buf_len,
              "k1=%s det=%d tab=%s cps=%d ranges_per_warp=%lld range_tail=%lld tail_ranges=%lld cnt_match=%d "
-             "cnt_cache=%d cnt_path=%d", c.k1_general ? "general" : "auto", c.det,
+             "cnt_cache=%d cnt_path=%d str=%d", c.k1_general ? "general" : "auto", c.det,
              c.tab == 1 ? "hyb" : (c.tab == 2 ? "fac" : "auto"), c.cps, c.ranges_per_warp, c.range_tail,
-             c.tail_ranges, c.cnt_match, c.cnt_cache, c.cnt_path);
+             c.tail_ranges, c.cnt_match, c.cnt_cache, c.cnt_path, c.str);
     return NRW_OK;
 }
 
@@ -282,7 +284,7 @@ extern "C" int nrw_guided_phases(int64_t n, int64_t range, int64_t warps, int64_
     return NRW_OK;
 }
 
-static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, WalkPlan* plan) {
+static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, WalkPlan* plan, bool allow_str = true) {
     if (!e || !t || !w) return fail(NRW_EINVAL, "nrw_walk_philox: NULL argument");
     if (t->n_rows <= 0 || t->n_live < 0 || t->n_live > t->n_rows)
         return fail(NRW_EINVAL, "nrw_walk_philox: n_rows=%d n_live=%d", t->n_rows, t->n_live);
@@ -357,6 +359,20 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
     if (w->count_tn && w->walker_hi - w->walker_lo >= (1ll << 32))
         return fail(NRW_EINVAL, "nrw_walk_philox: count_tn bins are 32-bit; walk fewer than 2^32 ids per launch");
 
+    // Structured draw (nrw_tables.rowinfo_str): taken by the trimmed score walk when the tables carry it.  Decided
+    // here because it changes what is staged (no alias patterns); if the launch then turns out not to qualify for
+    // the trimmed kernel (histogram too large for shared memory ...) the plan is redone without it.
+    bool k1s_horizon_ok;
+    {   // the trimmed kernel keeps 32-bit running sums per lane: walks so long that even a 32-id range could wrap
+        // them stay with the general kernel
+        long long mw = 3;
+        if (p.cwpack != 0x03020100u) for (int i = 0; i < 4; ++i) mw = std::max(mw, (long long)((p.cwpack >> (8 * i)) & 0xffu));
+        k1s_horizon_ok = 32ll * (long long)w->nt * mw < (1ll << 31);
+    }
+    const bool str = allow_str && e->cfg.str && w->sampler == NRW_SAMPLER_ALIAS && t->alias_layout == NRW_ALIAS_COMPACT &&
+                     t->rowinfo_str && (w->score || w->node_hist) && !w->count_tn && !w->score_sq && !w->time_weight &&
+                     w->nt >= 2 && !e->cfg.k1_general && e->cfg.cps != 2 && k1s_horizon_ok;
+
     // table location
     int smem = 16, tab;
     if (w->sampler == NRW_SAMPLER_CDF) {
@@ -375,10 +391,10 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
         } else if (t->alias_layout == NRW_ALIAS_COMPACT) {
             if (t->n_alias > (1 << 15))
                 return fail(NRW_EINVAL, "nrw_walk_philox: compact layout holds <= 2^15 alias entries");
-            const int ab = table_bytes(t->n_alias, 8), rb = table_bytes(t->n_rows, 8);
+            const int ab = str ? 0 : table_bytes(t->n_alias, 8), rb = table_bytes(t->n_rows, 8);
             // factored row descriptors (fluence-structured meshes): taken when the descriptor table
             // does not fit shared memory but the three small tables do; NRW_TAB=hyb / fac overrides
-            const bool have_fac = t->fac_dir && t->fac_tail && t->fac_cls && t->fac_period > 1 &&
+            const bool have_fac = (str ? (t->fac_dir_str && t->fac_tail_str) : (t->fac_dir && t->fac_tail)) && t->fac_cls && t->fac_period > 1 &&
                                   t->fac_cells > 0 && t->fac_n_tail == t->n_rows - t->n_live &&
                                   (long long)t->fac_period * t->fac_cells == t->n_live;
             const long long fbl = have_fac ? (long long)table_bytes(t->fac_period, 8) + table_bytes(t->fac_n_tail, 8) +
@@ -404,6 +420,10 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
                 p.sm_fdir = smem; smem += align16(t->fac_period * 8);
                 p.sm_ftail = smem; smem += align16(t->fac_n_tail * 8);
                 p.sm_fcls = smem; smem += align16(((t->n_live + 15) / 16) * 4);
+            }
+            if (str) {           // the structured descriptors in place of the alias ones; no alias patterns are staged
+                p.rowinfo = t->rowinfo_str; p.n_alias = 0; p.str_thr = t->str_thresh;
+                if (tab == TAB_FAC) { p.fac_dir = t->fac_dir_str; p.fac_tail = t->fac_tail_str; p.fac_exit_w0 = t->fac_exit_w0_str; }
             }
         } else {
             return fail(NRW_EINVAL, "nrw_walk_philox: alias_layout=%d", t->alias_layout);
@@ -478,14 +498,8 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
     if ((tl == TL_SCORE || tl == TL_HIST_S || tl == (TL_SCORE | TL_HIST_S)) && !w->score_sq && w->nt >= 2 &&
         tab_compact(tab)) {
         const bool hist = (tl & TL_HIST_S) != 0;
-        bool general = e->cfg.k1_general != 0;
+        const bool general = e->cfg.k1_general != 0 || !k1s_horizon_ok;
         const bool idw = p.cwpack == 0x03020100u;
-        {   // the trimmed kernel keeps 32-bit running sums per lane (see below): walks so long that even a
-            // 32-id range could wrap them stay with the general kernel
-            long long mw = 3;
-            if (!idw) for (int i = 0; i < 4; ++i) mw = std::max(mw, (long long)((p.cwpack >> (8 * i)) & 0xffu));
-            if (32ll * (long long)w->nt * mw >= (1ll << 31)) general = true;
-        }
         const bool det = e->cfg.det != 0;                    // NRW_DET=0: draw on deterministic rows too
         if (!general) {
             // a lane's 32-bit step and score sums are flushed at every range fetch: keep
@@ -502,7 +516,16 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
             // since (C1 mesh, 9e5 .. 1.35e8 walkers): more warps draw more tickets for no gain in issue rate
             const int cps = (plan->smem <= 112 * 1024 && e->cfg.cps == 2) ? 2 : 1;
 #define Y(TAB, IDW, DET, CPS)                                                       \
-    if (tab == TAB && idw == IDW && det == DET && cps == CPS) {                     \
+    if (tab == TAB && idw == IDW && det == DET && cps == CPS && str && CPS == 1) {  \
+        if (hist) {                                                                 \
+            plan->fn = (const void*)walk_score_kernel<TAB, IDW, DET, 1, true, false, true>;  \
+            plan->name = "walk_score_hist_str<" #TAB "," #IDW "," #DET ",cps=1>";   \
+        } else {                                                                    \
+            plan->fn = (const void*)walk_score_kernel<TAB, IDW, DET, 1, false, false, true>; \
+            plan->name = "walk_score_str<" #TAB "," #IDW "," #DET ",cps=1>";        \
+        }                                                                           \
+    }                                                                               \
+    if (tab == TAB && idw == IDW && det == DET && cps == CPS && !str) {             \
         if (hist) {                                                                 \
             plan->fn = (const void*)walk_score_kernel<TAB, IDW, DET, CPS, true>;    \
             plan->name = "walk_score_hist<" #TAB "," #IDW "," #DET ",cps=" #CPS ">"; \
@@ -529,6 +552,8 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
 #undef Y
         }
     }
+    // the structured descriptors were staged for the trimmed walk; any other kernel needs the alias tables
+    if (str && strncmp(plan->name, "walk_score", 10) != 0) return make_plan(e, t, w, plan, false);
     // time-resolved counts through the likely paths, nothing else tallied, compact tables: the trimmed walk too
     if (tl == TL_CNT_G && p.cnt_path && tab_compact(tab) && w->nt >= 2 && !e->cfg.k1_general &&
         32ll * (long long)w->nt < (1ll << 31)) {

@@ -65,6 +65,7 @@ struct WalkParams {
     // most likely trajectory of every start (nrw_walk.count_path): walkers still on it are tallied through a per-CTA
     // histogram of the steps at which walkers LEAVE it (sm_left: n_starts x (t_cap + 1)); path staged at sm_path
     const int32_t* cnt_path; int sm_path, sm_left;
+    uint32_t str_thr;                            // structured draw (walk_score.cuh, STR): the one alias threshold
     // TAB_FAC (tables.py::FactoredRows): live row k = i + j * fac_period; sources of the staged tables
     const void* fac_dir; const void* fac_tail; const void* fac_cls;
     int fac_period, fac_cells, fac_n_tail, fac_shift;

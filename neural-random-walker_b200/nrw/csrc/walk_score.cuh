@@ -65,7 +65,11 @@ __device__ __forceinline__ uint2 philox2x32_10_rk(uint32_t c0, uint32_t c1, cons
 // (nrw_walk.count_path, see walk_philox.cuh): a walker still on its start's path is not tallied step by step --
 // one shared-memory atomic records the step at which it leaves the path and the epilogue credits the path bins
 // from the suffix sums of that histogram; steps off the path go to their (diffuse) bins with plain REDs.
-template <int TAB, bool IDW, bool DET, int CPS, bool HIST = false, bool CNT = false>
+// STR: structured draw (include/nrw.h, nrw_tables.rowinfo_str): the row descriptor carries the row's own direction
+// `same` where the pattern offset was, and  target = base + (coin <= p.str_thr ? slot : same)  -- the alias
+// draw's target for every (slot, coin), verified entry by entry on the host -- needs no alias look-up: one
+// shared-memory load per step instead of two dependent ones, and no alias patterns to stage.
+template <int TAB, bool IDW, bool DET, int CPS, bool HIST = false, bool CNT = false, bool STR = false>
 __global__ void __launch_bounds__(CPS == 1 ? 1024 : 768, CPS)
 walk_score_kernel(const __grid_constant__ WalkParams p) {
     static_assert(tab_compact(TAB), "compact alias tables only");
@@ -126,7 +130,8 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
         else atomicAdd(hist_s + k, c);
     };
     auto det_target = [&](uint32_t w0, uint32_t w1) -> int {     // the single successor of a detabs row
-        return (int)(row_base(w1) + (alias_s[row_off(w0)].y & 0xffffu));
+        if constexpr (STR) return (int)(row_base(w1) + row_off(w0));
+        else return (int)(row_base(w1) + (alias_s[row_off(w0)].y & 0xffffu));
     };
     auto flush_score = [&]() {
         if (p.score && s >= 0 && x != 0)
@@ -281,9 +286,14 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
         };
         auto step = [&](uint32_t slot, uint32_t coin) {
             const int tn = t + 1;
-            const uint2 e = alias_s[row_off(ra) + slot];
             // target row; rb still carries its flag bits, which the descriptor look-up drops (load_row2)
-            const uint32_t knew = rb + ((coin <= e.x) ? (e.y & 0xffffu) : (e.y >> 16));
+            uint32_t knew;
+            if constexpr (STR) {
+                knew = rb + ((coin <= p.str_thr) ? slot : row_off(ra));
+            } else {
+                const uint2 e = alias_s[row_off(ra) + slot];
+                knew = rb + ((coin <= e.x) ? (e.y & 0xffffu) : (e.y >> 16));
+            }
             const uint2 row = load_row2<TAB>(p, rowinfo_a, knew);
             ra = row.x; rb = row.y;
             if constexpr (CNT) {

@@ -40,7 +40,9 @@ class _Tables(C.Structure):
                 ("fac_period", C.c_int32), ("fac_cells", C.c_int32), ("fac_n_tail", C.c_int32),
                 ("fac_shift", C.c_int32), ("fac_magic", C.c_uint32), ("fac_exit_w0", C.c_uint32),
                 ("fac_exit_base", C.c_uint32),
-                ("tree", C.c_void_p), ("tree_ptr", C.c_void_p)]
+                ("tree", C.c_void_p), ("tree_ptr", C.c_void_p),
+                ("rowinfo_str", C.c_void_p), ("str_thresh", C.c_uint32), ("fac_exit_w0_str", C.c_uint32),
+                ("fac_dir_str", C.c_void_p), ("fac_tail_str", C.c_void_p)]
 
 
 class _Reduce(C.Structure):
@@ -327,6 +329,18 @@ class Engine:
                 st.fac_shift, st.fac_magic = fr.shift, fr.magic
                 st.fac_exit_w0, st.fac_exit_base = fr.exit_w0, fr.exit_base
                 keep_fac = fac
+            # structured form of the same tables (fluence matrices): the score walk then draws without alias look-ups
+            sr = _tables.structure_rows(at) if at.layout == "compact" else None
+            if sr is not None:
+                ri_str = self._dev(sr[0], np.uint32)
+                st.rowinfo_str, st.str_thresh = _ptr(ri_str), int(sr[1])
+                keep_fac = keep_fac + (ri_str,)
+                fs = _tables.factorise_rows(at, csr.n_live, rowinfo=sr[0]) if fr is not None else None
+                if fs is not None and (fs.period, fs.cells, fs.shift, fs.magic, fs.exit_base) == (
+                        fr.period, fr.cells, fr.shift, fr.magic, fr.exit_base) and np.array_equal(fs.cls_bits, fr.cls_bits):
+                    fac_s = (self._dev(fs.dirtab, np.uint32), self._dev(fs.tail, np.uint32))
+                    st.fac_dir_str, st.fac_tail_str, st.fac_exit_w0_str = _ptr(fac_s[0]), _ptr(fac_s[1]), fs.exit_w0
+                    keep_fac = keep_fac + fac_s
         max_class = 0 if node_class is None else int(np.asarray(node_class).max(initial=0))
         return DeviceTables(csr, indptr, cols, vals, cum, nc, at, rowinfo, alias_t, st, max_class, keep_fac)
 

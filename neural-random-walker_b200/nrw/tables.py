@@ -119,14 +119,72 @@ class FactoredRows:
         return np.stack([w0.astype(np.uint32), base.astype(np.uint32)], axis=1)
 
 
-def factorise_rows(at: "AliasTables", n_live: int):
-    """FactoredRows of compact alias tables whose row descriptors have the (direction, cell)
-    structure of the fluence mesh (fluence_mini_app.py:331-381: row r = i + j (ND-1), a stay row
-    reaches all directions of one other cell, an exit row reaches the sink), or None.  Nothing is
-    assumed: the factored form is accepted only if it reproduces every descriptor bit for bit."""
+def structure_rows(at: "AliasTables"):
+    """The alias tables of a fluence matrix have a closed form: a stay row keeps the walker's direction with
+    probability 1 - pone and else scatters it uniformly over the ND-1 directions of the new cell
+    (fluence_mini_app.py:368-371), so Vose's construction pairs every slot with the row's own direction `same`:
+    entry s = (T, own = s, alias = same) with ONE threshold T for the whole mesh, and entry `same` always yields
+    `same`.  A draw (slot, coin) then needs no table:  target = base + (coin <= T ? slot : same).
+
+    Returns ``(rowinfo_str, T)`` -- the compact row descriptors with `same` in the 15-bit pattern-offset field --
+    or None.  Nothing is assumed: every entry of every pattern is compared with the closed form, so the structured
+    draw returns the alias draw's target for EVERY (slot, coin) -- the same trajectories bit for bit."""
     if at.layout != "compact":
         return None
     ri = at.rowinfo
+    w0 = ri[:, 0]
+    n = ((w0 >> np.uint32(ROW_N_SHIFT)) & np.uint32(0x3FF)).astype(np.int64)
+    off = (w0 & np.uint32(0x7FFF)).astype(np.int64)
+    th = at.alias[:, 0].astype(np.int64)
+    own = (at.alias[:, 1] & np.uint32(0xFFFF)).astype(np.int64)
+    ali = (at.alias[:, 1] >> np.uint32(16)).astype(np.int64)
+    live = n > 0
+    if not live.any():
+        return None
+    T = None
+    same_of = {}
+    for o, k in set(zip(off[live].tolist(), n[live].tolist())):         # one check per (pattern, length)
+        e = slice(o, o + k)
+        if o + k > len(th) or not np.array_equal(own[e], np.arange(k)):
+            return None
+        certain = (th[e] == 0xFFFFFFFF) | (ali[e] == own[e])              # entries whose outcome is their own slot
+        if k == 1:
+            if not certain[0]:
+                return None
+            same_of[(o, k)] = 0
+            continue
+        cand = np.nonzero(certain)[0]
+        if len(cand) != 1:
+            return None
+        same = int(cand[0])
+        rest = np.arange(k) != same
+        if not (ali[e][rest] == same).all():
+            return None
+        ts = np.unique(th[e][rest])
+        if len(ts) != 1 or (T is not None and int(ts[0]) != T):
+            return None
+        T = int(ts[0])
+        same_of[(o, k)] = same
+    if T is None:
+        T = 0xFFFFFFFF                                                    # only single-successor rows: no coin matters
+    same = np.zeros(len(w0), dtype=np.uint32)
+    key = off * 1024 + n                                                  # one key per (pattern, length)
+    keys, inv = np.unique(key[live], return_inverse=True)
+    same[live] = np.array([same_of[(int(k) // 1024, int(k) % 1024)] for k in keys], dtype=np.uint32)[inv]
+    out = ri.copy()
+    out[:, 0] = (w0 & ~np.uint32(0x7FFF)) | same
+    return np.ascontiguousarray(out), T
+
+
+def factorise_rows(at: "AliasTables", n_live: int, rowinfo=None):
+    """FactoredRows of compact alias tables whose row descriptors have the (direction, cell)
+    structure of the fluence mesh (fluence_mini_app.py:331-381: row r = i + j (ND-1), a stay row
+    reaches all directions of one other cell, an exit row reaches the sink), or None.  Nothing is
+    assumed: the factored form is accepted only if it reproduces every descriptor bit for bit.
+    ``rowinfo``: another descriptor array of the same tables (the structured one, ``structure_rows``)."""
+    if at.layout != "compact":
+        return None
+    ri = at.rowinfo if rowinfo is None else rowinfo
     n_rows = ri.shape[0]
     n_tail = n_rows - n_live
     if n_live < 2 or not (1 <= n_tail <= 64):

@@ -36,7 +36,7 @@ def pytest_collection_modifyitems(config, items):
 
 
 SWITCHES = ("NRW_K1", "NRW_DET", "NRW_TAB", "NRW_CPS", "NRW_RANGES_PER_WARP", "NRW_RANGE_TAIL", "NRW_TAIL_RANGES",
-            "NRW_CNT_MATCH", "NRW_CNT_CACHE", "NRW_CNT_PATH")
+            "NRW_CNT_MATCH", "NRW_CNT_CACHE", "NRW_CNT_PATH", "NRW_STR")
 
 
 class _EnginePerSwitches:

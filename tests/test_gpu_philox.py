@@ -209,7 +209,7 @@ def test_fused_solve_path_equals_the_general_launch(engine, c1_csr):
         ref = {seed: solve_fluence(*args, source=source, rng="philox", seed=seed, want_stderr=True) for seed in (3, 4)}
         for seed in (3, 4, 3):
             res = solve_fluence(*args, source=source, rng="philox", seed=seed)
-            assert res.stderr is None and "walk_score<" in res.kernel
+            assert res.stderr is None and "walk_score" in res.kernel
             assert np.array_equal(res.per_start, ref[seed].per_start)
             assert np.array_equal(res.rwSol, ref[seed].rwSol)
             assert res.walker_steps == ref[seed].walker_steps
@@ -325,6 +325,14 @@ def k1_env(monkeypatch):
         monkeypatch.delenv("NRW_K1", raising=False)
         monkeypatch.delenv("NRW_DET", raising=False)
         monkeypatch.delenv("NRW_CPS", raising=False)
+        # "fast*": the trimmed kernel on the alias tables (NRW_STR=0); "str*": its structured draw, which the
+        # planner takes by default wherever the tables have the closed form of the fluence matrix
+        if variant.startswith("str"):
+            monkeypatch.delenv("NRW_STR", raising=False)
+        else:
+            monkeypatch.setenv("NRW_STR", "0")
+        if variant == "str_nodet":
+            monkeypatch.setenv("NRW_DET", "0")
         if variant == "fast_cps2":
             monkeypatch.setenv("NRW_CPS", "2")
         if variant == "general":
@@ -334,7 +342,7 @@ def k1_env(monkeypatch):
     return set_variant
 
 
-@pytest.mark.parametrize("variant", ["fast", "fast_cps2", "fast_nodet", "general"])
+@pytest.mark.parametrize("variant", ["fast", "fast_cps2", "fast_nodet", "general", "str", "str_nodet"])
 def test_score_fast_path_bit_exact_all_variants(engine, c1_csr, k1_env, variant):
     """walk_score_kernel and the general kernel produce the same integers as the numpy port:
     identity and packed class weights, ragged starts with the sink and empty starts in the list,
@@ -345,7 +353,7 @@ def test_score_fast_path_bit_exact_all_variants(engine, c1_csr, k1_env, variant)
     _, nc1, _ = _classes(c1_csr, mesh.source_default)                    # classes {0, 1}
     nc3 = (np.arange(c1_csr.n_rows) % 4).astype(np.uint8)                # classes {0, 1, 2, 3}
     nc3[900] = 2                                                         # a weighted sink
-    want = "walk_philox<" if variant == "general" else "walk_score<TAB_SMEM"
+    want = "walk_philox<" if variant == "general" else ("walk_score_str<TAB_SMEM" if variant.startswith("str") else "walk_score<TAB_SMEM")
     starts = np.array([435, 0, 900, 14, 14, 899, 450, 16, 464])
     counts = np.array([3000, 0, 17, 1, 333, 64, 5, 2500, 1200])
     total = int(counts.sum())
@@ -361,7 +369,7 @@ def test_score_fast_path_bit_exact_all_variants(engine, c1_csr, k1_env, variant)
                 assert want in res.kernel, res.kernel
                 if variant != "general":
                     assert (",true," if idw else ",false,") in res.kernel, res.kernel
-                    assert (",false,cps=" if variant == "fast_nodet" else ",true,cps=") in res.kernel, res.kernel
+                    assert (",false,cps=" if variant in ("fast_nodet", "str_nodet") else ",true,cps=") in res.kernel, res.kernel
                     assert res.kernel.endswith("cps=2>" if variant == "fast_cps2" else "cps=1>"), res.kernel
             else:
                 assert "walk_philox<" in res.kernel                      # nt = 1: no step at all
@@ -371,7 +379,8 @@ def test_score_fast_path_bit_exact_all_variants(engine, c1_csr, k1_env, variant)
             res = engine.walk(tabs, starts, counts, nt, 5, score=True, class_value=cv, walker_range=rng_,
                               start_id_base=idb, node_hist=True)                  # + occupancy histogram
             if nt >= 2:
-                assert ("walk_philox<" if variant == "general" else "walk_score_hist<TAB_SMEM") in res.kernel
+                assert ("walk_philox<" if variant == "general" else "walk_score_hist_str<TAB_SMEM"
+                        if variant.startswith("str") else "walk_score_hist<TAB_SMEM") in res.kernel
             _cmp(res, port, hist=True)
     # a long uniform start list: many range fetches and start changes per warp
     tabs = engine.upload(c1_csr, node_class=nc1)
@@ -398,9 +407,15 @@ def test_score_fast_path_hybrid_tables_and_survivors(engine, k1_env, monkeypatch
                 monkeypatch.setenv("NRW_TAB", mode)
             else:
                 monkeypatch.delenv("NRW_TAB", raising=False)
-            res = engine.walk(tabs, starts, 48, nt, 6, score=True, class_value=[0, 1, 0, 0])
-            assert want in res.kernel, res.kernel
-            _cmp(res, port, hist=False)
+            for st in ("0", None):                       # alias tables, then the structured draw on the same modes
+                if st:
+                    monkeypatch.setenv("NRW_STR", st)
+                else:
+                    monkeypatch.delenv("NRW_STR", raising=False)
+                res = engine.walk(tabs, starts, 48, nt, 6, score=True, class_value=[0, 1, 0, 0])
+                assert (want if st else want.replace("walk_score<", "walk_score_str<")) in res.kernel, res.kernel
+                _cmp(res, port, hist=False)
+            monkeypatch.setenv("NRW_STR", "0")
     assert port["counters"]["survivors"] > 0
 
 
@@ -410,7 +425,7 @@ def _full_size_scores(engine, k1_env, variants):
     _, nc, _ = _classes(csr, mesh.source_default)
     tabs = engine.upload(csr, node_class=nc)
     out = {}
-    for variant in ("fast", "fast_nodet", "general"):
+    for variant in variants:
         k1_env(variant)
         r = engine.walk(tabs, np.arange(10000), 1000, 30000, 3, score=True, class_value=[0, 1, 0, 0])
         out[variant] = (r.score.cpu().numpy(), r.counters_dict(), r.kernel)
@@ -419,9 +434,9 @@ def _full_size_scores(engine, k1_env, variants):
 
 def test_score_fast_path_equals_general_kernel_at_full_size(engine, k1_env):
     """C5 mesh, 1e7 walkers: the trimmed kernel and the general kernel agree on every score."""
-    out = _full_size_scores(engine, k1_env, ("fast", "fast_nodet", "general"))
-    assert "walk_score<" in out["fast"][2] and "walk_philox<" in out["general"][2]
-    for v in ("fast", "fast_nodet"):
+    out = _full_size_scores(engine, k1_env, ("fast", "fast_nodet", "general", "str", "str_nodet"))
+    assert "walk_score<" in out["fast"][2] and "walk_philox<" in out["general"][2] and "walk_score_str<" in out["str"][2]
+    for v in ("fast", "fast_nodet", "str", "str_nodet"):
         assert np.array_equal(out[v][0], out["general"][0])
         assert out[v][1] == out["general"][1]
 
@@ -585,7 +600,7 @@ def test_factored_row_descriptors_equal_the_table(engine, c1_csr, k1_env, monkey
     for nc, cv in ((nc1, [0, 1, 0, 0]), (nc3, [5, 0, 255, 1])):
         tabs = engine.upload(c1_csr, node_class=nc)
         assert tabs.factored and tabs.struct.fac_period == 30 and tabs.struct.fac_cells == 30
-        for variant in ("fast", "fast_nodet", "general"):
+        for variant in ("fast", "fast_nodet", "general", "str", "str_nodet"):
             k1_env(variant)
             monkeypatch.setenv("NRW_TAB", "fac")
             for nt in (64, 3, 2):
@@ -643,4 +658,4 @@ def test_very_long_time_horizons_stay_with_the_general_kernel(engine, c1_csr):
     port = philox_port.walk_port(c1_csr, starts, counts, 1 << 23, 3, alias=tabs.alias_host, class_value=[0, 255, 0, 0])
     _cmp(res, port, hist=False)
     res = engine.walk(tabs, starts, counts, 1 << 18, 3, score=True, class_value=[0, 255, 0, 0])
-    assert "walk_score<" in res.kernel, res.kernel
+    assert "walk_score" in res.kernel, res.kernel

@@ -55,7 +55,7 @@ def test_c5_fluence_per_cell_against_the_reference_chain(engine, c5):
     unit = C5["v"] * C5["dt"] * 3.0
     for M, l2_max in ((12500, None), (100000, 1e-2)):
         res = solve_fluence(csr, M, nt, 0, C5["dt"], C5["v"], rng="philox", seed=77 + M)
-        assert "walk_score<TAB_SMEM" in res.kernel
+        assert "walk_score_str<TAB_SMEM" in res.kernel          # the structured draw (fluence tables)
         _check(expectation.fluence_error_stats(res.per_start, mean, var, M, unit), l2_max)
         # mean walk length: walker-steps (the throughput unit) against the chain's expected draw count
         want = steps.sum() * M
@@ -111,7 +111,7 @@ def test_c4_refined_mesh_fluence_against_the_reference_chain(engine):
     tabs = engine.upload(csr, node_class=nc)
     starts = np.arange(0, csr.n_live, 7)
     res = engine.walk(tabs, starts, M, nt, 21, score=True, class_value=(cv != 0).astype(float))
-    assert "walk_score<TAB_FAC" in res.kernel, res.kernel
+    assert "walk_score_str<TAB_FAC" in res.kernel, res.kernel
     unit = C4["v"] * C4["dt"] * float(cv[cv != 0][0])
     per_start = res.score.cpu().numpy().astype(np.float64) * unit / M
     stats = expectation.fluence_error_stats(per_start, mean[starts], var[starts], M, unit)

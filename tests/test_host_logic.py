@@ -375,3 +375,39 @@ def test_launch_descriptors_build_without_a_device(c1_csr):
     assert tabs.struct.tree == tabs.tree[0].data_ptr() and tabs.tree_host[1][-1] == len(tabs.tree_host[0])
     with pytest.raises(E.NrwError):                      # the library refuses a NULL engine: no launch happened
         eng.prepare_walk(tabs, [435], 5, 40, 3, score=True, class_value=[0, 1, 0, 0])
+
+
+def test_structured_rows_reproduce_every_alias_draw(c1_csr):
+    """nrw.tables.structure_rows: target = base + (coin <= T ? slot : same) must be the alias draw's target for EVERY
+    (slot, coin) of every row -- checked here exhaustively over the slots and at the coin values around the
+    thresholds -- on the default mesh, the bench mesh and a mesh with factored descriptors; tables without the
+    closed form (a general graph, a tampered entry) are refused."""
+    from nrw import mesh, tables
+    for csr in (c1_csr, mesh.build_fluence_csr(0.01, 0.02, 200, 0.15, 1), mesh.build_fluence_csr(0.001, 1.0 / 31.0, 200, 0.15, 1)):
+        nc = (np.arange(csr.n_rows) % 3).astype(np.uint8)
+        at = tables.build_alias(csr, node_class=nc)
+        ri_s, T = tables.structure_rows(at)
+        w0, w1 = at.rowinfo[:, 0].astype(np.int64), at.rowinfo[:, 1].astype(np.int64)
+        assert np.array_equal(ri_s[:, 1], at.rowinfo[:, 1]) and np.array_equal(ri_s[:, 0] >> 15, at.rowinfo[:, 0] >> 15)
+        n, off, same = (w0 >> 15) & 0x3FF, w0 & 0x7FFF, ri_s[:, 0].astype(np.int64) & 0x7FFF
+        th = at.alias[:, 0].astype(np.int64)
+        own, ali = (at.alias[:, 1] & 0xFFFF).astype(np.int64), (at.alias[:, 1] >> 16).astype(np.int64)
+        rows = np.repeat(np.arange(csr.n_rows), n)
+        slot = np.arange(len(rows)) - np.repeat(np.cumsum(n) - n, n)
+        e = off[rows] + slot
+        for coin in (0, T - 1, T, T + 1, 0xFFFFFFFF):
+            alias_t = np.where(coin <= th[e], own[e], ali[e])
+            str_t = np.where(coin <= T, slot, same[rows])
+            assert np.array_equal(alias_t, str_t), coin
+        fr = tables.factorise_rows(at, csr.n_live, rowinfo=ri_s)
+        assert fr is not None and np.array_equal(fr.synthesise(csr.n_live), ri_s[:csr.n_live])
+    # no closed form: a general graph, and a fluence table with one alias target changed
+    q = np.random.default_rng(1).dirichlet(np.ones(6), size=6)
+    assert tables.structure_rows(tables.build_alias(mesh.csr_from_dense(q, n_live=5))) is None
+    at = tables.build_alias(c1_csr)
+    k = int(at.rowinfo[435, 0] & 0x7FFF) + 3
+    at.alias[k, 1] = (at.alias[k, 1] & 0xFFFF) | (((at.alias[k, 1] >> 16) ^ 1) << 16)
+    assert tables.structure_rows(at) is None
+    at = tables.build_alias(c1_csr)
+    at.alias[k, 0] -= 1                                     # a second threshold
+    assert tables.structure_rows(at) is None

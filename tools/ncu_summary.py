@@ -50,7 +50,8 @@ def plan_name(ncu_name):
         tab, idw, det, cps, hist = args[:5]
         if len(args) > 5 and args[5]:
             return "walk_count<%s>" % TAB_NAMES[tab]
-        return "%s<%s,%s,%s,cps=%d>" % ("walk_score_hist" if hist else "walk_score", TAB_NAMES[tab],
+        strv = "_str" if len(args) > 6 and args[6] else ""
+        return "%s%s<%s,%s,%s,cps=%d>" % ("walk_score_hist" if hist else "walk_score", strv, TAB_NAMES[tab],
                                         "true" if idw else "false", "true" if det else "false", cps)
     m = re.search(r"walk_philox_kernel<\(?(?:int\))?(\d+), \(?(?:int\))?(\d+)>", ncu_name)
     if m:
