@@ -625,9 +625,13 @@ def e2e_leg(eng, tabs, csr, starts, Mg, id_base, rank, world, dev, args, barrier
     h_score = torch.zeros(n_nodes, dtype=torch.int64).pin_memory()
     h_cnt = torch.zeros(8, dtype=torch.int64).pin_memory()
 
+    sr = at.structured()
+    h_str = pin(sr[0]) if sr is not None else None
+
     class _View:           # AliasTables-like view over the pinned copies
         layout, n_alias = "compact", at.n_alias
         rowinfo, alias = h_row.numpy(), h_alias.numpy()
+        rowinfo_str, str_thresh = (h_str.numpy(), sr[1]) if sr is not None else (None, 0)
     ex = ndist.TallyExchange(n_nodes, eng) if world > 1 else None
     if ex is not None and not ex.fused:
         return {"value": None, "unit": METRIC, "unavailable": "no peer memory between the ranks: the host entry needs the fused exchange"}
@@ -646,7 +650,10 @@ def e2e_leg(eng, tabs, csr, starts, Mg, id_base, rank, world, dev, args, barrier
     e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
     if world > 1:
         tdist.all_reduce(e2e_s, op=tdist.ReduceOp.MAX)
-    h2d = h_row.numel() * 4 + h_alias.numel() * 4 + h_starts.numel() * 4 + h_prefix.numel() * 8 + h_idbase.numel() * 8
+    # structured tables: only the structured descriptors are copied (the walk reads nothing else)
+    tab_bytes = h_str.numel() * 4 if (h_str is not None and "_str<" in tabs_kernel_hint(eng, tabs, starts, Mg)) else \
+        h_row.numel() * 4 + h_alias.numel() * 4
+    h2d = tab_bytes + h_starts.numel() * 4 + h_prefix.numel() * 8 + h_idbase.numel() * 8
     d2h = h_score.numel() * 8 + 72
     return {"value": float(e2e_steps) / float(e2e_s.item()), "unit": METRIC,
             "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "steps": n_e2e,
@@ -654,6 +661,12 @@ def e2e_leg(eng, tabs, csr, starts, Mg, id_base, rank, world, dev, args, barrier
             "entry": "nrw_fluence_scores_host (pinned host buffers)%s" %
                      ("; every rank uploads its inputs, the walk sums over ranks in its tail, every rank reads the "
                       "REDUCED scores back" if world > 1 else "")}
+
+
+def tabs_kernel_hint(eng, tabs, starts, Mg):
+    """Name of the kernel the planner picks for the score walk on these tables (tells whether the structured draw runs)."""
+    _, r = eng.prepare_walk(tabs, starts, Mg, NT, seed=1, class_value=[0, 1, 0, 0], score=True)
+    return r.kernel
 
 
 def run_args_leg(rank, world, barrier):

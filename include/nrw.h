@@ -301,10 +301,14 @@ NRW_API int  nrw_expand_counts(nrw_engine* e, const uint32_t* count_tn, int32_t 
  * score / counters back and synchronises `stream`.  `reduce` NULL: single GPU, the engine's own
  * tally buffer.  With `reduce` (N > 1; n must be n_starts + NRW_N_COUNTERS): the walk tallies into
  * reduce->own_buf + offset, the sums over ranks come back from reduce->own_buf + out_offset, and the call
- * fails with NRW_ECUDA if a peer timed out.  start_id_base_host may be NULL.                */
+ * fails with NRW_ECUDA if a peer timed out.  start_id_base_host may be NULL.  rowinfo_str_host / str_thresh:
+ * the structured form of the same tables (nrw_tables.rowinfo_str; nrw/tables.py::structure_rows) or NULL / 0;
+ * when given and the planner takes the structured walk, ONLY it is copied (n_rows * 8 bytes instead of
+ * descriptors + alias patterns) -- same results.                                              */
 NRW_API int  nrw_fluence_scores_host(nrw_engine* e,
                              int32_t n_rows, int32_t n_live, int32_t n_alias,
                              const void* rowinfo_host, const void* alias_host,
+                             const void* rowinfo_str_host, uint32_t str_thresh,
                              int32_t n_starts, const int32_t* start_nodes_host,
                              const int64_t* start_prefix_host, const int64_t* start_id_base_host,
                              int64_t walker_lo, int64_t walker_hi, uint64_t seed, int32_t nt,
@@ -333,6 +337,7 @@ NRW_API int  nrw_fluence_scores_host(nrw_engine* e,
 NRW_API int  nrw_fluence_scores_host_static(nrw_engine* e,
                              int32_t n_rows, int32_t n_live, int32_t n_alias,
                              const void* rowinfo_host, const void* alias_host,
+                             const void* rowinfo_str_host, uint32_t str_thresh,
                              int32_t n_starts, const int32_t* start_nodes_host,
                              const int64_t* start_prefix_host, const int64_t* start_id_base_host,
                              int64_t walker_lo, int64_t walker_hi, uint64_t seed, int32_t nt,

@@ -659,8 +659,31 @@ static int grow(void** buf, size_t* cap, size_t need) {
     return NRW_OK;
 }
 
+// H2D of the transition tables of a host-buffer solve: a dry plan says which form the walk will read -- the
+// structured descriptors alone (t->rowinfo_str, staged where the descriptors go) or descriptors + alias patterns --
+// and only that form is copied; t->rowinfo_str is cleared when the alias form is taken.
+static int stage_tables_host(nrw_engine* e, nrw_tables* t, const nrw_walk* w, const void* rowinfo_host,
+                             const void* alias_host, const void* rowinfo_str_host, cudaStream_t st) {
+    bool use_str = false;
+    if (rowinfo_str_host) {
+        WalkPlan probe;
+        const int rc = make_plan(e, t, w, &probe);
+        if (rc) return rc;
+        use_str = strncmp(probe.name, "walk_score_str", 14) == 0 || strncmp(probe.name, "walk_score_hist_str", 19) == 0;
+    }
+    if (use_str) {
+        CUDA_TRY(cudaMemcpyAsync((void*)t->rowinfo_str, rowinfo_str_host, (size_t)t->n_rows * 8, cudaMemcpyHostToDevice, st));
+    } else {
+        t->rowinfo_str = nullptr;
+        CUDA_TRY(cudaMemcpyAsync((void*)t->rowinfo, rowinfo_host, (size_t)t->n_rows * 8, cudaMemcpyHostToDevice, st));
+        CUDA_TRY(cudaMemcpyAsync((void*)t->alias, alias_host, (size_t)t->n_alias * 8, cudaMemcpyHostToDevice, st));
+    }
+    return NRW_OK;
+}
+
 extern "C" int nrw_fluence_scores_host(nrw_engine* e, int32_t n_rows, int32_t n_live, int32_t n_alias,
                                        const void* rowinfo_host, const void* alias_host,
+                                       const void* rowinfo_str_host, uint32_t str_thresh,
                                        int32_t n_starts, const int32_t* start_nodes_host,
                                        const int64_t* start_prefix_host, const int64_t* start_id_base_host,
                                        int64_t walker_lo, int64_t walker_hi, uint64_t seed, int32_t nt,
@@ -681,12 +704,6 @@ extern "C" int nrw_fluence_scores_host(nrw_engine* e, int32_t n_rows, int32_t n_
     if ((rc = grow(&e->d_starts, &e->cap_starts, (size_t)n_starts * 4))) return rc;
     if ((rc = grow(&e->d_prefix, &e->cap_prefix, (size_t)(n_starts + 1) * 8))) return rc;
     if (start_id_base_host && (rc = grow(&e->d_idbase, &e->cap_idbase, (size_t)n_starts * 8))) return rc;
-    CUDA_TRY(cudaMemcpyAsync(e->d_rowinfo, rowinfo_host, (size_t)n_rows * 8, cudaMemcpyHostToDevice, st));
-    CUDA_TRY(cudaMemcpyAsync(e->d_alias, alias_host, (size_t)n_alias * 8, cudaMemcpyHostToDevice, st));
-    CUDA_TRY(cudaMemcpyAsync(e->d_starts, start_nodes_host, (size_t)n_starts * 4, cudaMemcpyHostToDevice, st));
-    CUDA_TRY(cudaMemcpyAsync(e->d_prefix, start_prefix_host, (size_t)(n_starts + 1) * 8, cudaMemcpyHostToDevice, st));
-    if (start_id_base_host)
-        CUDA_TRY(cudaMemcpyAsync(e->d_idbase, start_id_base_host, (size_t)n_starts * 8, cudaMemcpyHostToDevice, st));
     long long* tally;                                           // scores, then the counters: one buffer
     if (reduce) {
         tally = (long long*)reduce->own_buf + reduce->offset;  // zeroed by the tail of the previous launch
@@ -699,6 +716,9 @@ extern "C" int nrw_fluence_scores_host(nrw_engine* e, int32_t n_rows, int32_t n_
     memset(&t, 0, sizeof(t));
     t.n_rows = n_rows; t.n_live = n_live; t.alias_layout = NRW_ALIAS_COMPACT; t.n_alias = n_alias;
     t.rowinfo = e->d_rowinfo; t.alias = e->d_alias;
+    // the structured form of the tables, when the caller has it (nrw_tables.rowinfo_str): it is staged in the
+    // descriptor buffer INSTEAD of descriptors + alias patterns if the planner takes the structured walk
+    if (rowinfo_str_host) { t.rowinfo_str = e->d_rowinfo; t.str_thresh = str_thresh; }
     nrw_walk w;
     memset(&w, 0, sizeof(w));
     w.n_starts = n_starts; w.start_nodes = (const int32_t*)e->d_starts;
@@ -717,6 +737,11 @@ extern "C" int nrw_fluence_scores_host(nrw_engine* e, int32_t n_rows, int32_t n_
     }
     w.counters = (unsigned long long*)(tally + n_starts);
     w.reduce = reduce;
+    if ((rc = stage_tables_host(e, &t, &w, rowinfo_host, alias_host, rowinfo_str_host, st))) return rc;
+    CUDA_TRY(cudaMemcpyAsync(e->d_starts, start_nodes_host, (size_t)n_starts * 4, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(e->d_prefix, start_prefix_host, (size_t)(n_starts + 1) * 8, cudaMemcpyHostToDevice, st));
+    if (start_id_base_host)
+        CUDA_TRY(cudaMemcpyAsync(e->d_idbase, start_id_base_host, (size_t)n_starts * 8, cudaMemcpyHostToDevice, st));
     if ((rc = nrw_walk_philox(e, &t, &w, stream))) return rc;
     const long long* result = (reduce && reduce->world > 1) ? (const long long*)reduce->own_buf + reduce->out_offset : tally;
     CUDA_TRY(cudaMemcpyAsync(score_host, result, (size_t)n_starts * 8, cudaMemcpyDeviceToHost, st));
@@ -759,6 +784,7 @@ static int static_scratch_base(int device, unsigned char** base) {
 
 extern "C" int nrw_fluence_scores_host_static(nrw_engine* e, int32_t n_rows, int32_t n_live, int32_t n_alias,
                                               const void* rowinfo_host, const void* alias_host,
+                                              const void* rowinfo_str_host, uint32_t str_thresh,
                                               int32_t n_starts, const int32_t* start_nodes_host,
                                               const int64_t* start_prefix_host, const int64_t* start_id_base_host,
                                               int64_t walker_lo, int64_t walker_hi, uint64_t seed, int32_t nt,
@@ -792,8 +818,6 @@ extern "C" int nrw_fluence_scores_host_static(nrw_engine* e, int32_t n_rows, int
     long long* tally = (long long*)(base + o_tally);
     // the array keeps the previous call's contents: ticket slot and tally must start at zero
     CUDA_TRY(cudaMemsetAsync(base + o_slot, 0, o_row, st));
-    CUDA_TRY(cudaMemcpyAsync(base + o_row, rowinfo_host, (size_t)n_rows * 8, cudaMemcpyHostToDevice, st));
-    CUDA_TRY(cudaMemcpyAsync(base + o_alias, alias_host, (size_t)n_alias * 8, cudaMemcpyHostToDevice, st));
     CUDA_TRY(cudaMemcpyAsync(base + o_starts, start_nodes_host, (size_t)n_starts * 4, cudaMemcpyHostToDevice, st));
     CUDA_TRY(cudaMemcpyAsync(base + o_prefix, start_prefix_host, ((size_t)n_starts + 1) * 8, cudaMemcpyHostToDevice, st));
     if (start_id_base_host)
@@ -802,6 +826,7 @@ extern "C" int nrw_fluence_scores_host_static(nrw_engine* e, int32_t n_rows, int
     memset(&t, 0, sizeof(t));
     t.n_rows = n_rows; t.n_live = n_live; t.alias_layout = NRW_ALIAS_COMPACT; t.n_alias = n_alias;
     t.rowinfo = base + o_row; t.alias = base + o_alias;
+    if (rowinfo_str_host) { t.rowinfo_str = base + o_row; t.str_thresh = str_thresh; }
     nrw_walk w;
     memset(&w, 0, sizeof(w));
     w.n_starts = n_starts; w.start_nodes = (const int32_t*)(base + o_starts);
@@ -818,6 +843,7 @@ extern "C" int nrw_fluence_scores_host_static(nrw_engine* e, int32_t n_rows, int
         for (int i = 0; i < 4; ++i) w.class_value[i] = ident ? (double)i : class_value[i];
     }
     w.counters = (unsigned long long*)(tally + n_starts);
+    if ((rc = stage_tables_host(e, &t, &w, rowinfo_host, alias_host, rowinfo_str_host, st))) return rc;
     // plan + launch as nrw_walk_philox does, with the ticket slot in the static array instead of the engine's ring
     WalkPlan plan;
     if ((rc = make_plan(e, &t, &w, &plan))) return rc;

@@ -111,10 +111,10 @@ def load_library():
     lib.nrw_assemble_events.argtypes = [vp, i32, vp, vp, vp, vp, vp, vp, dbl, dbl, vp, i32, i32, vp, vp]
     lib.nrw_expand_events.argtypes = [vp, i64, vp, vp, vp, i32, i32, vp, vp]
     lib.nrw_expand_counts.argtypes = [vp, vp, i32, i32, i32, i32, i64, vp, vp]
-    lib.nrw_fluence_scores_host.argtypes = [vp, i32, i32, i32, vp, vp, i32, vp, vp, vp, i64, i64, u64,
+    lib.nrw_fluence_scores_host.argtypes = [vp, i32, i32, i32, vp, vp, vp, C.c_uint32, i32, vp, vp, vp, i64, i64, u64,
                                             i32, C.POINTER(dbl * 4), vp, vp, C.POINTER(_Reduce), vp]
-    lib.nrw_fluence_scores_host_static.argtypes = [vp, i32, i32, i32, vp, vp, i32, vp, vp, vp, i64, i64, u64,
-                                                   i32, C.POINTER(dbl * 4), vp, vp, vp]
+    lib.nrw_fluence_scores_host_static.argtypes = [vp, i32, i32, i32, vp, vp, vp, C.c_uint32, i32, vp, vp, vp, i64, i64,
+                                                   u64, i32, C.POINTER(dbl * 4), vp, vp, vp]
     lib.nrw_microbench.argtypes = [vp, i32, i32, i32, vp, vp, vp, vp]
     lib.nrw_p2p_allreduce_i64.argtypes = [vp, vp, vp, i64, i64, i64, i64, i32, i32, u64, vp, vp]
     lib.nrw_guided_phases.argtypes = [i64, i64, i64, i64, i64, vp, vp, vp, C.POINTER(i32)]
@@ -330,7 +330,7 @@ class Engine:
                 st.fac_exit_w0, st.fac_exit_base = fr.exit_w0, fr.exit_base
                 keep_fac = fac
             # structured form of the same tables (fluence matrices): the score walk then draws without alias look-ups
-            sr = _tables.structure_rows(at) if at.layout == "compact" else None
+            sr = at.structured() if at.layout == "compact" else None
             if sr is not None:
                 ri_str = self._dev(sr[0], np.uint32)
                 st.rowinfo_str, st.str_thresh = _ptr(ri_str), int(sr[1])
@@ -628,8 +628,15 @@ class Engine:
         keep = (alias_tables.rowinfo, alias_tables.alias, start_nodes, start_prefix, score_out, counters_out, cv,
                 start_id_base, exchange)
         fn, check, handle, stream = self.lib.nrw_fluence_scores_host, self._check, self.handle, self.stream
+        # the structured form of the tables, when they have one (`rowinfo_str` / `str_thresh` attributes of the view,
+        # or AliasTables.structured()): the walk then needs half the table bytes on the device
+        ri_str, thr = getattr(alias_tables, "rowinfo_str", None), int(getattr(alias_tables, "str_thresh", 0))
+        if ri_str is None and hasattr(alias_tables, "structured") and alias_tables.structured() is not None:
+            ri_str, thr = alias_tables.structured()
+        keep = keep + (ri_str,)
         head = (handle, int(n_rows), int(n_live), int(alias_tables.n_alias),
                 C.c_void_p(alias_tables.rowinfo.ctypes.data), C.c_void_p(alias_tables.alias.ctypes.data),
+                C.c_void_p(ri_str.ctypes.data) if ri_str is not None else None, thr,
                 len(start_nodes), C.c_void_p(start_nodes.ctypes.data), C.c_void_p(start_prefix.ctypes.data),
                 C.c_void_p(start_id_base.ctypes.data) if start_id_base is not None else None,
                 int(walker_lo), int(walker_hi))

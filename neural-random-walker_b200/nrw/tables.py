@@ -83,6 +83,12 @@ class AliasTables:
     def n_alias(self) -> int:
         return int(self.alias.shape[0])
 
+    def structured(self):
+        """``structure_rows(self)`` computed once: (rowinfo_str, threshold) or None."""
+        if not hasattr(self, "_structured"):
+            self._structured = structure_rows(self)
+        return self._structured
+
 
 @dataclass
 class FactoredRows:
