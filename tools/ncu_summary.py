@@ -95,7 +95,8 @@ def traffic_json(h, data, out_path, argv):
              "smem_bank_conflict_share": (val("l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum") or 0.0)
                                          / max(val("l1tex__data_pipe_lsu_wavefronts_mem_shared.sum") or 1.0, 1.0)}
     if argv.get("bench_line"):
-        line = json.loads(open(argv["bench_line"]).read().strip().splitlines()[-1])
+        # the last JSON line of the log (under ncu the log ends with ncu's own ==PROF== lines)
+        line = json.loads([l for l in open(argv["bench_line"]).read().splitlines() if l.startswith("{")][-1])
         facts["walker_steps_per_launch"] = int(line["roofline"]["walker_steps_per_launch"])
         assert line["roofline"]["kernel"] == facts["kernel"], (line["roofline"]["kernel"], facts["kernel"])
         facts["warp_inst_per_32_walker_steps"] = 32.0 * facts["warp_inst_per_launch"] / facts["walker_steps_per_launch"]
