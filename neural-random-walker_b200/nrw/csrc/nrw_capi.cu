@@ -50,6 +50,7 @@ struct nrw_config {
     int cnt_cache;         // NRW_CNT_CACHE=0: no CTA-level cache of hot bins
     int cnt_path;          // NRW_CNT_PATH=0: ignore nrw_walk.count_path
     int str;               // NRW_STR=0: ignore nrw_tables.rowinfo_str (alias look-ups in the score walk)
+    int block;             // NRW_BLOCK: threads per CTA of the trimmed walk (1024; fewer = an occupancy experiment)
 };
 
 struct nrw_engine {
@@ -90,6 +91,8 @@ static nrw_config config_from_env() {
     c.cnt_cache = env_int("NRW_CNT_CACHE", 1) != 0;
     c.cnt_path = env_int("NRW_CNT_PATH", 1) != 0;
     c.str = env_int("NRW_STR", 1) != 0;
+    c.block = env_int("NRW_BLOCK", WALK_THREADS);
+    if (c.block < 32 || c.block > WALK_THREADS || c.block % 32) c.block = WALK_THREADS;
     return c;
 }
 
@@ -143,9 +146,9 @@ extern "C" int nrw_engine_config(nrw_engine* e, char* buf, int buf_len) {
     const nrw_config& c = e->cfg;
     snprintf(buf, (size_t)buf_len,
              "k1=%s det=%d tab=%s cps=%d ranges_per_warp=%lld range_tail=%lld tail_ranges=%lld cnt_match=%d "
-             "cnt_cache=%d cnt_path=%d str=%d", c.k1_general ? "general" : "auto", c.det,
+             "cnt_cache=%d cnt_path=%d str=%d block=%d", c.k1_general ? "general" : "auto", c.det,
              c.tab == 1 ? "hyb" : (c.tab == 2 ? "fac" : "auto"), c.cps, c.ranges_per_warp, c.range_tail,
-             c.tail_ranges, c.cnt_match, c.cnt_cache, c.cnt_path, c.str);
+             c.tail_ranges, c.cnt_match, c.cnt_cache, c.cnt_path, c.str, c.block);
     return NRW_OK;
 }
 
@@ -313,6 +316,7 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
     p.key = seed_to_key(w->seed); p.nt = w->nt;
     for (int r = 0; r < 10; ++r) p.rk[r] = p.key + (uint32_t)r * PHILOX_W32;
     p.t_last = w->nt - 1;
+    p.t_fast = w->nt > 4 ? (uint32_t)(w->nt - 4) : 0u;
     p.score = (long long*)w->score; p.score_sq = w->score_sq; p.tw = w->time_weight;
     p.cwpack = 0;
     for (int i = 0; i < 4; ++i) {
@@ -539,6 +543,13 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
             Y2(TAB_SMEM, true, false) Y2(TAB_SMEM, false, false) Y2(TAB_HYB, true, false) Y2(TAB_HYB, false, false)
             Y2(TAB_FAC, true, true) Y2(TAB_FAC, false, true) Y2(TAB_FAC, true, false) Y2(TAB_FAC, false, false)
 #undef Y2
+            if (cps == 1 && e->cfg.block != WALK_THREADS) {        // occupancy experiment: fewer warps per SM
+                plan->block = e->cfg.block;
+                long long r1 = n / ((long long)plan->grid * (plan->block / 32) * rpw);
+                r1 = (r1 / 32) * 32;
+                p.range = r1 < 32 ? 32 : (r1 > 4096 ? 4096 : r1);
+                while (p.range > 32 && p.range * (long long)w->nt * maxw >= (1ll << 31)) p.range = ((p.range / 2) / 32) * 32;
+            }
             if (cps == 2) {
                 plan->block = 768;
                 long long g2 = (n + 767) / 768;

@@ -46,6 +46,7 @@ struct WalkParams {
     uint32_t key; int nt;
     uint32_t rk[10];                             // Philox round keys key + r * W32
     int t_last;                                  // nt - 1
+    uint32_t t_fast;                             // max(nt - 4, 0): a step pair that starts at t < t_fast ends before step nt - 2
     long long* score; double* score_sq;
     uint32_t cwpack; double cv[4]; const double* tw;
     unsigned long long* node_hist;

@@ -29,6 +29,7 @@
 //     them up one by one account for them in the take.  NRW_DET=0 disables it.
 // Requires nt >= 2 (the planner sends nt = 1 to the general kernel).
 #pragma once
+#include <type_traits>
 #include "walk_philox.cuh"
 
 namespace nrw {
@@ -214,14 +215,16 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
         const unsigned need = __ballot_sync(NRW_FULL_MASK, dead);
         const uint32_t off = cur + (uint32_t)__popc(need & lt_mask);
         const uint32_t ncur = cur + (uint32_t)__popc(need);
-        if (ncur <= end) {
-            // DET: the whole warp is idle inside a deterministic-exit start (nothing there ever enters the
-            // step phase): account for every id the range and the start still hold in one go, lane L
-            // standing for ids cur + L, cur + L + 32, ...  (No `continue` after it: every lane is still dead and
-            // falls through the step phase; a second loop back-edge cost 1 % -- 0.523 -> 0.517 ms on C5.)
-            bool bulk = false;
-            if constexpr (DET) bulk = need == NRW_FULL_MASK && __all_sync(NRW_FULL_MASK, det_n != 0u && off < s_end_off);
-            if (bulk) {
+        // hot: the range holds an id for every dead lane and (DET) at least one lane is walking -- one test, one branch
+        if (ncur <= end && (!DET || need != NRW_FULL_MASK)) [[likely]] {
+            cur = ncur;
+            if (dead) take(off);
+        } else if (ncur <= end) {
+            // DET: the whole warp is idle.  Inside a deterministic-exit start (nothing there ever enters the step
+            // phase) it accounts for every id the range and the start still hold in one go, lane L standing for ids
+            // cur + L, cur + L + 32, ...  (No `continue` after it: every lane is still dead and falls through the
+            // step phase; a second loop back-edge cost 1 % -- 0.523 -> 0.517 ms on C5.)
+            if (__all_sync(NRW_FULL_MASK, det_n != 0u && off < s_end_off)) {
                 const uint32_t lim = min(end, s_end_off);
                 const uint32_t k = (lim - cur - (uint32_t)lane + 31u) >> 5;
                 x += det_w * k;
@@ -230,7 +233,7 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
                 cur = lim;
             } else {
                 cur = ncur;
-                if (dead) take(off);
+                take(off);
             }
         } else {
             // cold (once per id range): serve what the range still holds, then fetch the next one;
@@ -284,7 +287,10 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
             atomicAdd(left_s + s * (p.t_cap + 1) + min(l, p.t_cap), 1u);
             onpath = false;
         };
-        auto step = [&](uint32_t slot, uint32_t coin) {
+        // NEAR: the pair may reach the last two steps of time (cold); the hot pair starts at t < p.t_fast = nt - 4, so
+        // neither of its steps can, and carries no end-of-time test at all
+        auto step = [&](auto near_c, uint32_t slot, uint32_t coin) -> bool {     // true: the walker goes on
+            constexpr bool NEAR = decltype(near_c)::value;
             const int tn = t + 1;
             // target row; rb still carries its flag bits, which the descriptor look-up drops (load_row2)
             uint32_t knew;
@@ -318,9 +324,11 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
                 } else {
                     t = tn;
                 }
-                return;
+                return t >= 0;
             }
-            if (tn >= t_last - 1) [[unlikely]] { near_end(row, knew, tn); return; }
+            if constexpr (NEAR) {
+                if (tn >= t_last - 1) { near_end(row, knew, tn); return t >= 0; }
+            }
             // Hot path, branch-free: this step and -- on a row whose single successor is absorbing (DET: the
             // fluence exit rows, fluence_mini_app.py:355-357; no draw could change that step) -- the exit step it
             // implies are both inside the sum; what they add to score and step count sits in the top bits of the
@@ -342,17 +350,24 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
             // the walk ends here when the row is absorbing or (DET) its single successor is
             const bool dead = (row.x & (DET ? ROW_TERM : ROW_N_MASK)) == (DET ? ROW_TERM : 0u);
             t = dead ? -1 : tn;
+            return !dead;                        // (the branch after the first step of a pair tests the flag itself)
         };
         // one Philox call serves the two steps of a pair (common.cuh, "paired draws"): lanes are refilled
         // only here, so every live lane is at an even t and the whole warp shares the call
-        if (t >= 0) {
+        auto pair = [&](auto near_c) {
             const uint2 r = philox2x32_10_rk(c0, chi_base | (uint32_t)(t + 1), p);
             const unsigned long long va = (unsigned long long)r.x * row_len(ra);
-            step((uint32_t)(va >> 32), (uint32_t)va);
-            if (t >= 0) {
+            if (step(near_c, (uint32_t)(va >> 32), (uint32_t)va)) {
                 const unsigned long long vb = (unsigned long long)r.y * row_len(ra);
-                step((uint32_t)(vb >> 32), (uint32_t)vb);
+                step(near_c, (uint32_t)(vb >> 32), (uint32_t)vb);
             }
+        };
+        if constexpr (CNT) {
+            if (t >= 0) pair(std::true_type{});
+        } else {
+            // one unsigned test: the lane holds a walker (t >= 0) AND both steps of the pair stay clear of the end of time
+            if ((uint32_t)t < p.t_fast) pair(std::false_type{});
+            else if (t >= 0) [[unlikely]] pair(std::true_type{});
         }
     }
 

@@ -27,9 +27,10 @@ def main():
     tabs = eng.upload(csr, node_class=nc)
     starts = np.arange(csr.n_live)
     flush = torch.empty(512 << 20, dtype=torch.uint8, device=eng.device)
-    knobs = ("NRW_CPS", "NRW_DET", "NRW_K1", "NRW_RANGE_TAIL", "NRW_TAIL_RANGES", "NRW_RANGES_PER_WARP")
+    knobs = ("NRW_CPS", "NRW_DET", "NRW_K1", "NRW_RANGE_TAIL", "NRW_TAIL_RANGES", "NRW_RANGES_PER_WARP", "NRW_BLOCK")
     configs = [("default", {}), ("cps2", {"NRW_CPS": "2"}), ("single_range_size", {"NRW_TAIL_RANGES": "0"}),
-               ("always_draw", {"NRW_DET": "0"}), ("general", {"NRW_K1": "general"})]
+               ("always_draw", {"NRW_DET": "0"}), ("general", {"NRW_K1": "general"}),
+               ("block768", {"NRW_BLOCK": "768"}), ("block512", {"NRW_BLOCK": "512"}), ("block256", {"NRW_BLOCK": "256"})]
     if len(sys.argv) > 3 and sys.argv[3] == "sweep":        # guided range sizes: smallest range x tail share
         configs = [("single_range_size", {"NRW_TAIL_RANGES": "0"}), ("general_control", {"NRW_K1": "general"})]
         for rt, tr in ((2048, 2), (1024, 2), (512, 2), (256, 2), (128, 2), (64, 2), (1024, 1), (1024, 3), (512, 1),
@@ -39,6 +40,9 @@ def main():
             for rt, tr in ((1024, 2), (512, 2), (1024, 3)):
                 configs.append(("rpw%d_min%d_x%d" % (rpw, rt, tr), {"NRW_RANGES_PER_WARP": str(rpw), "NRW_RANGE_TAIL": str(rt),
                                                                      "NRW_TAIL_RANGES": str(tr)}))
+    only = os.environ.get("NRW_VARIANTS")                   # e.g. "default,always_draw": a subset by name
+    if only:
+        configs = [c for c in configs if c[0] in only.split(",")]
     for tag, env in configs:
         # the library reads its switches once per engine: one engine per variant (device tables are shared)
         sw = {k: None for k in knobs}
@@ -57,7 +61,7 @@ def main():
         torch.cuda.synchronize()
         ms = float(np.mean([a.elapsed_time(b) for a, b in ev]))
         steps = int(res.counters.cpu()[0].item())
-        print(json.dumps({"mesh": which, "M": M, "variant": tag, "kernel": res.kernel, "geometry": res.launch_geometry,
+        print(json.dumps({"lib": os.path.basename(os.environ.get("NRW_LIB", "libnrw.so")), "mesh": which, "M": M, "variant": tag, "kernel": res.kernel, "geometry": res.launch_geometry,
                           "kernel_ms": ms, "walker_steps": steps, "walker_steps_per_s": steps / (ms * 1e-3),
                           "score_sum": int(res.score.sum().item()),
                           "score_crc": int((res.score.cpu().numpy().astype(np.uint64) * (np.arange(len(starts), dtype=np.uint64) * np.uint64(2654435761) + np.uint64(1))).sum() & np.uint64(0xFFFFFFFFFFFF))}), flush=True)
