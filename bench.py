@@ -631,7 +631,7 @@ def e2e_leg(eng, tabs, csr, starts, Mg, id_base, rank, world, dev, args, barrier
     class _View:           # AliasTables-like view over the pinned copies
         layout, n_alias = "compact", at.n_alias
         rowinfo, alias = h_row.numpy(), h_alias.numpy()
-        rowinfo_str, str_thresh = (h_str.numpy(), sr[1]) if sr is not None else (None, 0)
+        rowinfo_str, str_thresh, str_n = (h_str.numpy(), sr[1], sr[2]) if sr is not None else (None, 0, 0)
     ex = ndist.TallyExchange(n_nodes, eng) if world > 1 else None
     if ex is not None and not ex.fused:
         return {"value": None, "unit": METRIC, "unavailable": "no peer memory between the ranks: the host entry needs the fused exchange"}

@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define NRW_ABI_VERSION 4
+#define NRW_ABI_VERSION 5
 
 #if defined(__GNUC__)
 #define NRW_API __attribute__((visibility("default")))
@@ -120,10 +120,15 @@ typedef struct nrw_tables {
      * look-up.  rowinfo_str = rowinfo with `same` in place of the pattern offset (w0 bits [0:15));
      * nrw/tables.py::structure_rows builds it and verifies every entry, so the structured draw yields the alias
      * draw's target for every (slot, coin).  The score walk takes it when present (one shared-memory look-up per
-     * step instead of two, no alias patterns staged).  fac_*_str: the factored form of rowinfo_str (period, cells,
+     * step instead of two, no alias patterns staged).  str_n: the one length of every row a walker can draw from
+     * when rows with a single absorbing successor are stepped without a draw -- all rows that are neither
+     * absorbing nor such a row (the stay rows of the fluence matrix all hold ND-1 entries); structure_rows
+     * verifies it and offers no structured form otherwise.  The walk then multiplies by a launch constant instead
+     * of extracting the length from the descriptor (ABI v5; must be >= 1 when rowinfo_str is given).  fac_*_str: the factored form of rowinfo_str (period, cells,
      * shift, magic, class bits and exit base are those of fac_*).  All NULL / 0 when absent.            */
     const void* rowinfo_str;  /* [n_rows] uint32 (w0, w1)                                   */
     uint32_t str_thresh;
+    uint32_t str_n;
     uint32_t fac_exit_w0_str;
     const void* fac_dir_str;  /* uint32 [fac_period][2]                                     */
     const void* fac_tail_str; /* uint32 [fac_n_tail][2]                                     */
@@ -301,14 +306,14 @@ NRW_API int  nrw_expand_counts(nrw_engine* e, const uint32_t* count_tn, int32_t 
  * score / counters back and synchronises `stream`.  `reduce` NULL: single GPU, the engine's own
  * tally buffer.  With `reduce` (N > 1; n must be n_starts + NRW_N_COUNTERS): the walk tallies into
  * reduce->own_buf + offset, the sums over ranks come back from reduce->own_buf + out_offset, and the call
- * fails with NRW_ECUDA if a peer timed out.  start_id_base_host may be NULL.  rowinfo_str_host / str_thresh:
- * the structured form of the same tables (nrw_tables.rowinfo_str; nrw/tables.py::structure_rows) or NULL / 0;
+ * fails with NRW_ECUDA if a peer timed out.  start_id_base_host may be NULL.  rowinfo_str_host / str_thresh / str_n:
+ * the structured form of the same tables (nrw_tables.rowinfo_str, .str_thresh, .str_n; nrw/tables.py::structure_rows) or NULL / 0 / 0;
  * when given and the planner takes the structured walk, ONLY it is copied (n_rows * 8 bytes instead of
  * descriptors + alias patterns) -- same results.                                              */
 NRW_API int  nrw_fluence_scores_host(nrw_engine* e,
                              int32_t n_rows, int32_t n_live, int32_t n_alias,
                              const void* rowinfo_host, const void* alias_host,
-                             const void* rowinfo_str_host, uint32_t str_thresh,
+                             const void* rowinfo_str_host, uint32_t str_thresh, uint32_t str_n,
                              int32_t n_starts, const int32_t* start_nodes_host,
                              const int64_t* start_prefix_host, const int64_t* start_id_base_host,
                              int64_t walker_lo, int64_t walker_hi, uint64_t seed, int32_t nt,
@@ -337,7 +342,7 @@ NRW_API int  nrw_fluence_scores_host(nrw_engine* e,
 NRW_API int  nrw_fluence_scores_host_static(nrw_engine* e,
                              int32_t n_rows, int32_t n_live, int32_t n_alias,
                              const void* rowinfo_host, const void* alias_host,
-                             const void* rowinfo_str_host, uint32_t str_thresh,
+                             const void* rowinfo_str_host, uint32_t str_thresh, uint32_t str_n,
                              int32_t n_starts, const int32_t* start_nodes_host,
                              const int64_t* start_prefix_host, const int64_t* start_id_base_host,
                              int64_t walker_lo, int64_t walker_hi, uint64_t seed, int32_t nt,

@@ -374,7 +374,7 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
         k1s_horizon_ok = 32ll * (long long)w->nt * mw < (1ll << 31);
     }
     const bool str = allow_str && e->cfg.str && w->sampler == NRW_SAMPLER_ALIAS && t->alias_layout == NRW_ALIAS_COMPACT &&
-                     t->rowinfo_str && (w->score || w->node_hist) && !w->count_tn && !w->score_sq && !w->time_weight &&
+                     t->rowinfo_str && t->str_n >= 1u && (w->score || w->node_hist) && !w->count_tn && !w->score_sq && !w->time_weight &&
                      w->nt >= 2 && !e->cfg.k1_general && e->cfg.cps != 2 && k1s_horizon_ok;
 
     // table location
@@ -426,7 +426,7 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
                 p.sm_fcls = smem; smem += align16(((t->n_live + 15) / 16) * 4);
             }
             if (str) {           // the structured descriptors in place of the alias ones; no alias patterns are staged
-                p.rowinfo = t->rowinfo_str; p.n_alias = 0; p.str_thr = t->str_thresh;
+                p.rowinfo = t->rowinfo_str; p.n_alias = 0; p.str_thr = t->str_thresh; p.str_n = t->str_n;
                 if (tab == TAB_FAC) { p.fac_dir = t->fac_dir_str; p.fac_tail = t->fac_tail_str; p.fac_exit_w0 = t->fac_exit_w0_str; }
             }
         } else {
@@ -694,7 +694,7 @@ static int stage_tables_host(nrw_engine* e, nrw_tables* t, const nrw_walk* w, co
 
 extern "C" int nrw_fluence_scores_host(nrw_engine* e, int32_t n_rows, int32_t n_live, int32_t n_alias,
                                        const void* rowinfo_host, const void* alias_host,
-                                       const void* rowinfo_str_host, uint32_t str_thresh,
+                                       const void* rowinfo_str_host, uint32_t str_thresh, uint32_t str_n,
                                        int32_t n_starts, const int32_t* start_nodes_host,
                                        const int64_t* start_prefix_host, const int64_t* start_id_base_host,
                                        int64_t walker_lo, int64_t walker_hi, uint64_t seed, int32_t nt,
@@ -729,7 +729,7 @@ extern "C" int nrw_fluence_scores_host(nrw_engine* e, int32_t n_rows, int32_t n_
     t.rowinfo = e->d_rowinfo; t.alias = e->d_alias;
     // the structured form of the tables, when the caller has it (nrw_tables.rowinfo_str): it is staged in the
     // descriptor buffer INSTEAD of descriptors + alias patterns if the planner takes the structured walk
-    if (rowinfo_str_host) { t.rowinfo_str = e->d_rowinfo; t.str_thresh = str_thresh; }
+    if (rowinfo_str_host) { t.rowinfo_str = e->d_rowinfo; t.str_thresh = str_thresh; t.str_n = str_n; }
     nrw_walk w;
     memset(&w, 0, sizeof(w));
     w.n_starts = n_starts; w.start_nodes = (const int32_t*)e->d_starts;
@@ -795,7 +795,7 @@ static int static_scratch_base(int device, unsigned char** base) {
 
 extern "C" int nrw_fluence_scores_host_static(nrw_engine* e, int32_t n_rows, int32_t n_live, int32_t n_alias,
                                               const void* rowinfo_host, const void* alias_host,
-                                              const void* rowinfo_str_host, uint32_t str_thresh,
+                                              const void* rowinfo_str_host, uint32_t str_thresh, uint32_t str_n,
                                               int32_t n_starts, const int32_t* start_nodes_host,
                                               const int64_t* start_prefix_host, const int64_t* start_id_base_host,
                                               int64_t walker_lo, int64_t walker_hi, uint64_t seed, int32_t nt,
@@ -837,7 +837,7 @@ extern "C" int nrw_fluence_scores_host_static(nrw_engine* e, int32_t n_rows, int
     memset(&t, 0, sizeof(t));
     t.n_rows = n_rows; t.n_live = n_live; t.alias_layout = NRW_ALIAS_COMPACT; t.n_alias = n_alias;
     t.rowinfo = base + o_row; t.alias = base + o_alias;
-    if (rowinfo_str_host) { t.rowinfo_str = base + o_row; t.str_thresh = str_thresh; }
+    if (rowinfo_str_host) { t.rowinfo_str = base + o_row; t.str_thresh = str_thresh; t.str_n = str_n; }
     nrw_walk w;
     memset(&w, 0, sizeof(w));
     w.n_starts = n_starts; w.start_nodes = (const int32_t*)(base + o_starts);

@@ -67,6 +67,8 @@ struct WalkParams {
     // histogram of the steps at which walkers LEAVE it (sm_left: n_starts x (t_cap + 1)); path staged at sm_path
     const int32_t* cnt_path; int sm_path, sm_left;
     uint32_t str_thr;                            // structured draw (walk_score.cuh, STR): the one alias threshold
+    uint32_t str_n;                              // ... and the one length of the rows a walker draws from (DET)
+    uint32_t zero;                               // 0 (walk_score.cuh adds it to its loop constants: they then stay in uniform registers)
     // TAB_FAC (tables.py::FactoredRows): live row k = i + j * fac_period; sources of the staged tables
     const void* fac_dir; const void* fac_tail; const void* fac_cls;
     int fac_period, fac_cells, fac_n_tail, fac_shift;

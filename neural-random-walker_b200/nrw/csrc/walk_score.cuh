@@ -45,15 +45,33 @@ __device__ __forceinline__ uint2 load_row2(const WalkParams& p, uint32_t rowinfo
 
 // Philox2x32-10 with the ten round keys read from the kernel parameters (constant bank operands of
 // the LOP3s) instead of being re-derived from the key in uniform registers every iteration.
-__device__ __forceinline__ uint2 philox2x32_10_rk(uint32_t c0, uint32_t c1, const WalkParams& p) {
+__device__ __forceinline__ uint2 philox2x32_10_rk(uint32_t c0, uint32_t c1, const uint32_t (&rk)[10]) {
 #pragma unroll
     for (int r = 0; r < 10; ++r) {
         const uint32_t hi = __umulhi(PHILOX_M2x32, c0);
         const uint32_t lo = PHILOX_M2x32 * c0;
-        c0 = hi ^ p.rk[r] ^ c1;
+        c0 = hi ^ rk[r] ^ c1;
         c1 = lo;
     }
     return make_uint2(c0, c1);
+}
+
+// The same with the first round key already folded into c1 (c1k = c1 ^ rk[0]).
+__device__ __forceinline__ uint2 philox2x32_10_k0(uint32_t c0, uint32_t c1k, const uint32_t (&rk)[10]) {
+    {
+        const uint32_t hi = __umulhi(PHILOX_M2x32, c0);
+        const uint32_t lo = PHILOX_M2x32 * c0;
+        c0 = hi ^ c1k;
+        c1k = lo;
+    }
+#pragma unroll
+    for (int r = 1; r < 10; ++r) {
+        const uint32_t hi = __umulhi(PHILOX_M2x32, c0);
+        const uint32_t lo = PHILOX_M2x32 * c0;
+        c0 = hi ^ rk[r] ^ c1k;
+        c1k = lo;
+    }
+    return make_uint2(c0, c1k);
 }
 
 // CPS = CTAs per SM: 1 -> 1024 threads (tables up to 227 KB), 2 -> two CTAs of 768 threads when the
@@ -96,6 +114,13 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
     const int sink_row = p.n_rows - 1;           // HIST: the node every exit ends on is counted in registers
 
     const int t_last = p.t_last;                 // nt - 1: last model step (fluence_mini_app.py:236); >= 1 here
+    // What the hot loop reads every iteration, as COMPUTED uniform values (p.zero is 0): a plain constant-bank operand
+    // is re-loaded into a uniform register in every iteration (five loads per step pair), a computed one stays there
+    const uint32_t zz = p.zero;
+    uint32_t rk[10];
+#pragma unroll
+    for (int r = 0; r < 10; ++r) rk[r] = p.rk[r] + zz;
+    const uint32_t t_fast = p.t_fast + zz, str_thr = p.str_thr + zz, str_n = p.str_n + zz;
     const uint32_t lt_mask = lanemask_lt();
 
     // ---- the lane's walker --------------------------------------------------------------------------
@@ -146,12 +171,12 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
         const long long d = s_end - rbase;
         s_end_off = d <= 0 ? 0u : (d > 0x7fffffffll ? 0x7fffffffu : (uint32_t)d);
         c0_base = (uint32_t)sid_base;
-        chi_base = (uint32_t)((unsigned long long)sid_base >> 32) << 24;
+        chi_base = ((uint32_t)((unsigned long long)sid_base >> 32) << 24) ^ rk[0];     // (with the first round key: pair)
         const uint32_t wrap_off = 0u - c0_base;              // c0_base + wrap_off == 2^32 (0: no wrap ahead)
         if (wrap_off != 0u && wrap_off < s_end_off) s_end_off = wrap_off;
     };
     auto pass_wrap = [&]() {
-        chi_base += 1u << 24;
+        chi_base = ((chi_base ^ rk[0]) + (1u << 24)) ^ rk[0];
         const long long d = s_end - rbase;
         s_end_off = d > 0x7fffffffll ? 0x7fffffffu : (uint32_t)d;
     };
@@ -182,15 +207,17 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
         rebase();
         if (off >= s_end_off) pass_wrap();       // the new start's ids wrapped before this lane's first one
         t_init = ((srow.x & ROW_N_MASK) == 0u) ? -1 : 0;       // started on the sink: an exit, no step
+        const uint32_t srow_w0 = srow.x;
+        if constexpr (STR && DET) srow.x = row_off(srow_w0);    // the take hands a new walker its direction (step below)
         if constexpr (DET) {
             // a start whose single successor is absorbing: every walker takes that one step (t = 1)
             // and exits; no draw can change it, so the take accounts for it and the lane stays free
-            const bool det = (srow.x & ROW_DETABS) != 0u;
+            const bool det = (srow_w0 & ROW_DETABS) != 0u;
             det_n = det ? 1u : 0u;
-            det_w = (det && t_last >= 2) ? weight_of(row_detcls(srow.x)) : 0u;   // t = nt-1 is outside the sum
+            det_w = (det && t_last >= 2) ? weight_of(row_detcls(srow_w0)) : 0u;   // t = nt-1 is outside the sum
             if (det) t_init = -1;
             if constexpr (HIST) {
-                det_tgt = det ? det_target(srow.x, srow.y) : 0;
+                det_tgt = det ? det_target(srow_w0, srow.y) : 0;
                 const bool in_sum = det && t_last >= 2;
                 det_hs = (in_sum && det_tgt == sink_row) ? 1u : 0u;
                 det_hn = (in_sum && det_tgt != sink_row) ? 1u : 0u;
@@ -294,14 +321,22 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
             const int tn = t + 1;
             // target row; rb still carries its flag bits, which the descriptor look-up drops (load_row2)
             uint32_t knew;
-            if constexpr (STR) {
-                knew = rb + ((coin <= p.str_thr) ? slot : row_off(ra));
+            uint32_t sel = 0;
+            if constexpr (STR && DET) {
+                // ra is the walker's DIRECTION, not its descriptor word: the offset a walker was sent to IS the `same`
+                // of the row it landed on (row = first row of the cell + direction; tables.structure_rows verifies it
+                // for every row a walker can draw from), and the length is the launch constant -- nothing of w0 is
+                // needed for the next draw
+                sel = (coin <= str_thr) ? slot : ra;
+                knew = rb + sel;
+            } else if constexpr (STR) {
+                knew = rb + ((coin <= str_thr) ? slot : row_off(ra));
             } else {
                 const uint2 e = alias_s[row_off(ra) + slot];
                 knew = rb + ((coin <= e.x) ? (e.y & 0xffffu) : (e.y >> 16));
             }
             const uint2 row = load_row2<TAB>(p, rowinfo_a, knew);
-            ra = row.x; rb = row.y;
+            ra = (STR && DET) ? sel : row.x; rb = row.y;
             if constexpr (CNT) {
                 const int k = (int)(knew & ROW_BASE_MASK);
                 if (tn < p.t_cap) {
@@ -354,11 +389,21 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
         };
         // one Philox call serves the two steps of a pair (common.cuh, "paired draws"): lanes are refilled
         // only here, so every live lane is at an even t and the whole warp shares the call
+        // length of the row the walker draws from.  STR && DET: a launch constant (nrw_tables.str_n) -- every row
+        // that is neither absorbing nor stepped without a draw has that length, so nothing is extracted from the
+        // descriptor and the multiply of the second step does not wait for the first step's look-up
+        auto rlen = [&](uint32_t w0) -> uint32_t {
+            if constexpr (STR && DET) return str_n;
+            else return row_len(w0);
+        };
         auto pair = [&](auto near_c) {
-            const uint2 r = philox2x32_10_rk(c0, chi_base | (uint32_t)(t + 1), p);
-            const unsigned long long va = (unsigned long long)r.x * row_len(ra);
+            // counter = (stream id low word, id bits 32..39 << 24 | t + 1); chi_base holds the id bits XOR the first round
+            // key (its low 24 bits are the key's: t + 1 < 2^24 enters by XOR as it would by OR), so the first round's
+            // "^ key ^ c1" is one three-input LOP3
+            const uint2 r = philox2x32_10_k0(c0, chi_base ^ (uint32_t)(t + 1), rk);
+            const unsigned long long va = (unsigned long long)r.x * rlen(ra);
             if (step(near_c, (uint32_t)(va >> 32), (uint32_t)va)) {
-                const unsigned long long vb = (unsigned long long)r.y * row_len(ra);
+                const unsigned long long vb = (unsigned long long)r.y * rlen(ra);
                 step(near_c, (uint32_t)(vb >> 32), (uint32_t)vb);
             }
         };
@@ -366,7 +411,7 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
             if (t >= 0) pair(std::true_type{});
         } else {
             // one unsigned test: the lane holds a walker (t >= 0) AND both steps of the pair stay clear of the end of time
-            if ((uint32_t)t < p.t_fast) pair(std::false_type{});
+            if ((uint32_t)t < t_fast) pair(std::false_type{});
             else if (t >= 0) [[unlikely]] pair(std::true_type{});
         }
     }

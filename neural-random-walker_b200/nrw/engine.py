@@ -41,7 +41,8 @@ class _Tables(C.Structure):
                 ("fac_shift", C.c_int32), ("fac_magic", C.c_uint32), ("fac_exit_w0", C.c_uint32),
                 ("fac_exit_base", C.c_uint32),
                 ("tree", C.c_void_p), ("tree_ptr", C.c_void_p),
-                ("rowinfo_str", C.c_void_p), ("str_thresh", C.c_uint32), ("fac_exit_w0_str", C.c_uint32),
+                ("rowinfo_str", C.c_void_p), ("str_thresh", C.c_uint32), ("str_n", C.c_uint32),
+                ("fac_exit_w0_str", C.c_uint32),
                 ("fac_dir_str", C.c_void_p), ("fac_tail_str", C.c_void_p)]
 
 
@@ -111,9 +112,9 @@ def load_library():
     lib.nrw_assemble_events.argtypes = [vp, i32, vp, vp, vp, vp, vp, vp, dbl, dbl, vp, i32, i32, vp, vp]
     lib.nrw_expand_events.argtypes = [vp, i64, vp, vp, vp, i32, i32, vp, vp]
     lib.nrw_expand_counts.argtypes = [vp, vp, i32, i32, i32, i32, i64, vp, vp]
-    lib.nrw_fluence_scores_host.argtypes = [vp, i32, i32, i32, vp, vp, vp, C.c_uint32, i32, vp, vp, vp, i64, i64, u64,
+    lib.nrw_fluence_scores_host.argtypes = [vp, i32, i32, i32, vp, vp, vp, C.c_uint32, C.c_uint32, i32, vp, vp, vp, i64, i64, u64,
                                             i32, C.POINTER(dbl * 4), vp, vp, C.POINTER(_Reduce), vp]
-    lib.nrw_fluence_scores_host_static.argtypes = [vp, i32, i32, i32, vp, vp, vp, C.c_uint32, i32, vp, vp, vp, i64, i64,
+    lib.nrw_fluence_scores_host_static.argtypes = [vp, i32, i32, i32, vp, vp, vp, C.c_uint32, C.c_uint32, i32, vp, vp, vp, i64, i64,
                                                    u64, i32, C.POINTER(dbl * 4), vp, vp, vp]
     lib.nrw_microbench.argtypes = [vp, i32, i32, i32, vp, vp, vp, vp]
     lib.nrw_p2p_allreduce_i64.argtypes = [vp, vp, vp, i64, i64, i64, i64, i32, i32, u64, vp, vp]
@@ -333,7 +334,7 @@ class Engine:
             sr = at.structured() if at.layout == "compact" else None
             if sr is not None:
                 ri_str = self._dev(sr[0], np.uint32)
-                st.rowinfo_str, st.str_thresh = _ptr(ri_str), int(sr[1])
+                st.rowinfo_str, st.str_thresh, st.str_n = _ptr(ri_str), int(sr[1]), int(sr[2])
                 keep_fac = keep_fac + (ri_str,)
                 fs = _tables.factorise_rows(at, csr.n_live, rowinfo=sr[0]) if fr is not None else None
                 if fs is not None and (fs.period, fs.cells, fs.shift, fs.magic, fs.exit_base) == (
@@ -628,15 +629,16 @@ class Engine:
         keep = (alias_tables.rowinfo, alias_tables.alias, start_nodes, start_prefix, score_out, counters_out, cv,
                 start_id_base, exchange)
         fn, check, handle, stream = self.lib.nrw_fluence_scores_host, self._check, self.handle, self.stream
-        # the structured form of the tables, when they have one (`rowinfo_str` / `str_thresh` attributes of the view,
-        # or AliasTables.structured()): the walk then needs half the table bytes on the device
+        # the structured form of the tables, when they have one (`rowinfo_str` / `str_thresh` / `str_n` attributes of
+        # the view, or AliasTables.structured()): the walk then needs half the table bytes on the device
         ri_str, thr = getattr(alias_tables, "rowinfo_str", None), int(getattr(alias_tables, "str_thresh", 0))
+        n_uni = int(getattr(alias_tables, "str_n", 0))
         if ri_str is None and hasattr(alias_tables, "structured") and alias_tables.structured() is not None:
-            ri_str, thr = alias_tables.structured()
+            ri_str, thr, n_uni = alias_tables.structured()
         keep = keep + (ri_str,)
         head = (handle, int(n_rows), int(n_live), int(alias_tables.n_alias),
                 C.c_void_p(alias_tables.rowinfo.ctypes.data), C.c_void_p(alias_tables.alias.ctypes.data),
-                C.c_void_p(ri_str.ctypes.data) if ri_str is not None else None, thr,
+                C.c_void_p(ri_str.ctypes.data) if ri_str is not None else None, thr, n_uni,
                 len(start_nodes), C.c_void_p(start_nodes.ctypes.data), C.c_void_p(start_prefix.ctypes.data),
                 C.c_void_p(start_id_base.ctypes.data) if start_id_base is not None else None,
                 int(walker_lo), int(walker_hi))

@@ -84,7 +84,7 @@ class AliasTables:
         return int(self.alias.shape[0])
 
     def structured(self):
-        """``structure_rows(self)`` computed once: (rowinfo_str, threshold) or None."""
+        """``structure_rows(self)`` computed once: (rowinfo_str, threshold, common row length) or None."""
         if not hasattr(self, "_structured"):
             self._structured = structure_rows(self)
         return self._structured
@@ -132,9 +132,12 @@ def structure_rows(at: "AliasTables"):
     entry s = (T, own = s, alias = same) with ONE threshold T for the whole mesh, and entry `same` always yields
     `same`.  A draw (slot, coin) then needs no table:  target = base + (coin <= T ? slot : same).
 
-    Returns ``(rowinfo_str, T)`` -- the compact row descriptors with `same` in the 15-bit pattern-offset field --
-    or None.  Nothing is assumed: every entry of every pattern is compared with the closed form, so the structured
-    draw returns the alias draw's target for EVERY (slot, coin) -- the same trajectories bit for bit."""
+    Returns ``(rowinfo_str, T, n_draw)`` -- the compact row descriptors with `same` in the 15-bit pattern-offset
+    field, the threshold, and the ONE length of every row a walker can draw from when rows with a single absorbing
+    successor are stepped without a draw (all rows that carry neither the `term` bit nor length 0: the stay rows of
+    the fluence matrix all hold ND-1 entries; nrw_tables.str_n) -- or None.  Nothing is assumed: every entry of every
+    pattern is compared with the closed form and the lengths are compared, so the structured draw returns the alias
+    draw's target for EVERY (slot, coin) -- the same trajectories bit for bit."""
     if at.layout != "compact":
         return None
     ri = at.rowinfo
@@ -173,13 +176,32 @@ def structure_rows(at: "AliasTables"):
         same_of[(o, k)] = same
     if T is None:
         T = 0xFFFFFFFF                                                    # only single-successor rows: no coin matters
+    draws = live & (((w0 >> np.uint32(ROW_TERM_BIT)) & np.uint32(1)) == 0)  # rows a walker is alive on (DET walk)
+    lens = np.unique(n[draws])
+    if len(lens) > 1:
+        return None                                                       # the walk multiplies by ONE length
+    n_draw = int(lens[0]) if len(lens) else 1
     same = np.zeros(len(w0), dtype=np.uint32)
     key = off * 1024 + n                                                  # one key per (pattern, length)
     keys, inv = np.unique(key[live], return_inverse=True)
     same[live] = np.array([same_of[(int(k) // 1024, int(k) % 1024)] for k in keys], dtype=np.uint32)[inv]
+    # The walk carries a walker's direction instead of its descriptor word (walk_score.cuh, STR && DET): the offset a
+    # walker is sent to must BE the `same` of the row it lands on, for every row it can draw from next -- on the
+    # fluence matrix row = first row of the cell + direction (fluence_mini_app.py:331-381).  Checked for every
+    # (row, slot) whose target is such a row.
+    base = (ri[:, 1] & np.uint32(ROW_BASE_MASK)).astype(np.int64)
+    src = np.nonzero(draws)[0]
+    if len(src):
+        tgt = (base[src][:, None] + np.arange(n_draw, dtype=np.int64)[None, :]).reshape(-1)
+        slot = np.tile(np.arange(n_draw, dtype=np.int64), len(src))
+        if tgt.max() >= len(w0):
+            return None
+        onward = draws[tgt]
+        if not np.array_equal(same[tgt[onward]].astype(np.int64), slot[onward]):
+            return None
     out = ri.copy()
     out[:, 0] = (w0 & ~np.uint32(0x7FFF)) | same
-    return np.ascontiguousarray(out), T
+    return np.ascontiguousarray(out), T, n_draw
 
 
 def factorise_rows(at: "AliasTables", n_live: int, rowinfo=None):

@@ -31,7 +31,7 @@ def test_library_exports_every_declared_symbol():
     for s in _declared_symbols():
         assert hasattr(lib, s), "libnrw.so does not export %s" % s
     assert set(_declared_symbols()) == set(engine.EXPORTS)
-    assert lib.nrw_abi_version() == 4
+    assert lib.nrw_abi_version() == 5
 
 
 def test_struct_mirrors_match_header_field_order():

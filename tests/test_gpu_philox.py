@@ -582,7 +582,7 @@ def test_host_buffer_entry_matches_device_walk(engine, c1_csr):
     check(Pinned, p_starts, p_prefix, p_score, p_cnt, 50, 50, 64, [0, 1, 0, 0], (7,))                  # empty window
     # the structured form of the tables beside them (only it is copied), pinned
     class PinnedStr(Pinned):
-        rowinfo_str, str_thresh = pinned(at.structured()[0]), at.structured()[1]
+        rowinfo_str, str_thresh, str_n = pinned(at.structured()[0]), at.structured()[1], at.structured()[2]
     check(PinnedStr, p_starts, p_prefix, p_score, p_cnt, 0, total, 64, [0, 1, 0, 0], (1, 2))
     check(PinnedStr, p_starts, p_prefix, p_score, p_cnt, 100, total - 7, 5, [0, 9, 0, 0], (4,))
     # pageable buffers and fresh result buffers (an AliasTables object: its structured form is found by itself)

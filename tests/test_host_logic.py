@@ -386,7 +386,7 @@ def test_structured_rows_reproduce_every_alias_draw(c1_csr):
     for csr in (c1_csr, mesh.build_fluence_csr(0.01, 0.02, 200, 0.15, 1), mesh.build_fluence_csr(0.001, 1.0 / 31.0, 200, 0.15, 1)):
         nc = (np.arange(csr.n_rows) % 3).astype(np.uint8)
         at = tables.build_alias(csr, node_class=nc)
-        ri_s, T = tables.structure_rows(at)
+        ri_s, T, n_draw = tables.structure_rows(at)
         w0, w1 = at.rowinfo[:, 0].astype(np.int64), at.rowinfo[:, 1].astype(np.int64)
         assert np.array_equal(ri_s[:, 1], at.rowinfo[:, 1]) and np.array_equal(ri_s[:, 0] >> 15, at.rowinfo[:, 0] >> 15)
         n, off, same = (w0 >> 15) & 0x3FF, w0 & 0x7FFF, ri_s[:, 0].astype(np.int64) & 0x7FFF
@@ -401,6 +401,10 @@ def test_structured_rows_reproduce_every_alias_draw(c1_csr):
             assert np.array_equal(alias_t, str_t), coin
         fr = tables.factorise_rows(at, csr.n_live, rowinfo=ri_s)
         assert fr is not None and np.array_equal(fr.synthesise(csr.n_live), ri_s[:csr.n_live])
+        # the one length of the rows a walker draws from (nrw_tables.str_n): every row that is neither absorbing nor
+        # a row whose single successor is absorbing (`term` bit)
+        alive_on = (n > 0) & (((w0 >> 26) & 1) == 0)
+        assert alive_on.any() and (n[alive_on] == n_draw).all() and n_draw == csr.meta["mesh"]["ND"] - 1
     # no closed form: a general graph, and a fluence table with one alias target changed
     q = np.random.default_rng(1).dirichlet(np.ones(6), size=6)
     assert tables.structure_rows(tables.build_alias(mesh.csr_from_dense(q, n_live=5))) is None
@@ -410,4 +414,18 @@ def test_structured_rows_reproduce_every_alias_draw(c1_csr):
     assert tables.structure_rows(at) is None
     at = tables.build_alias(c1_csr)
     at.alias[k, 0] -= 1                                     # a second threshold
+    assert tables.structure_rows(at) is None
+    # rows of two lengths that a walker can draw from: a mesh whose structure holds entry by entry but whose walk
+    # cannot multiply by one length is refused too
+    at = tables.build_alias(c1_csr)
+    r = int(np.nonzero(((at.rowinfo[:, 0] >> 15) & 0x3FF) > 1)[0][0])
+    at.rowinfo[r, 0] -= np.uint32(1 << 15)                  # one entry fewer (its last slot is never drawn)
+    sr = tables.structure_rows(at)
+    assert sr is None
+    # two stay rows of one cell trade places: every entry still has the closed form, but a walker sent to offset i no
+    # longer lands on the row whose own direction is i -- the walk carries that offset as the direction, so: refused
+    at = tables.build_alias(c1_csr)
+    stay = np.nonzero(((at.rowinfo[:, 0] >> 15) & 0x3FF) > 1)[0]
+    a = int(stay[np.nonzero(np.diff(stay) == 1)[0][0]])
+    at.rowinfo[[a, a + 1]] = at.rowinfo[[a + 1, a]]
     assert tables.structure_rows(at) is None

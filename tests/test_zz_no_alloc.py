@@ -37,6 +37,7 @@ def _call(lib, fn_name, handle, csr, at, starts, prefix, id_base, seed, nt, cv, 
     sr = at.structured() if use_str else None                  # the structured form of the tables, or without it
     head = (handle, csr.n_rows, csr.n_live, at.n_alias, C.c_void_p(at.rowinfo.ctypes.data),
             C.c_void_p(at.alias.ctypes.data), C.c_void_p(sr[0].ctypes.data) if sr else None, sr[1] if sr else 0,
+            sr[2] if sr else 0,
             len(starts), C.c_void_p(starts.ctypes.data),
             C.c_void_p(prefix.ctypes.data), C.c_void_p(id_base.ctypes.data) if id_base is not None else None,
             int(prefix[0] if lo is None else lo), int(prefix[-1] if hi is None else hi), seed, nt, C.byref(cvv),
@@ -94,14 +95,14 @@ def test_static_scratch_entry_refuses_what_does_not_fit():
     cv = (C.c_double * 4)(0, 1, 0, 0)
     p = C.c_void_p(tiny.ctypes.data)
     # the refined mesh (158 761 rows: 1.27 MB of descriptors alone) does not fit
-    rc = lib.nrw_fluence_scores_host_static(h, 158761, 158760, 8001, p, p, None, 0, 100, p, p, None, 0, 100, 1, 64,
+    rc = lib.nrw_fluence_scores_host_static(h, 158761, 158760, 8001, p, p, None, 0, 0, 100, p, p, None, 0, 100, 1, 64,
                                             C.byref(cv), p, p, None)
     msg = lib.nrw_last_error().decode()
     assert rc == -3 and str(STATIC_BYTES) in msg and "158761" in msg, (rc, msg)
     # ... nor does a start list of 60 000 entries on a small mesh
-    rc = lib.nrw_fluence_scores_host_static(h, 901, 900, 930, p, p, None, 0, 60000, p, p, p, 0, 100, 1, 64,
+    rc = lib.nrw_fluence_scores_host_static(h, 901, 900, 930, p, p, None, 0, 0, 60000, p, p, p, 0, 100, 1, 64,
                                             C.byref(cv), p, p, None)
     assert rc == -3, lib.nrw_last_error().decode()
     # bad arguments are EINVAL, as in the allocating entry
-    assert lib.nrw_fluence_scores_host_static(None, 901, 900, 930, p, p, None, 0, 10, p, p, None, 0, 10, 1, 64,
+    assert lib.nrw_fluence_scores_host_static(None, 901, 900, 930, p, p, None, 0, 0, 10, p, p, None, 0, 10, 1, 64,
                                               C.byref(cv), p, p, None) == -1
