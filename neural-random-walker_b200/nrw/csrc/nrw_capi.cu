@@ -69,6 +69,7 @@ struct nrw_engine {
     void* d_prefix; size_t cap_prefix;
     void* d_idbase; size_t cap_idbase;
     void* d_tally; size_t cap_tally;                          // scores, then NRW_N_COUNTERS counters
+    long long* h_tail;                                        // pinned: counters (+ exchange status) of a host-buffer solve
 };
 
 static int env_int(const char* name, int dflt) {
@@ -120,9 +121,11 @@ extern "C" int nrw_create(int device, nrw_engine** out) {
     e->next_slot = 0;
     e->d_rowinfo = e->d_alias = e->d_starts = e->d_prefix = e->d_idbase = e->d_tally = nullptr;
     e->cap_rowinfo = e->cap_alias = e->cap_starts = e->cap_prefix = e->cap_idbase = e->cap_tally = 0;
+    e->h_tail = nullptr;
     const size_t slot_bytes = (size_t)NRW_TICKET_SLOTS * TICKET_WORDS * sizeof(unsigned long long);
     cudaError_t err = cudaMalloc(&e->slots, slot_bytes);
     if (err == cudaSuccess) err = cudaMemset(e->slots, 0, slot_bytes);
+    if (err == cudaSuccess) err = cudaHostAlloc((void**)&e->h_tail, (NRW_N_COUNTERS + 2) * sizeof(long long), cudaHostAllocDefault);
     if (err != cudaSuccess) {
         nrw_destroy(e);                                   // frees whatever was allocated
         return fail(NRW_ECUDA, "nrw_create: cudaMalloc failed: %s", cudaGetErrorString(err));
@@ -135,6 +138,7 @@ extern "C" int nrw_destroy(nrw_engine* e) {
     if (!e) return NRW_OK;
     cudaSetDevice(e->device);
     cudaFree(e->slots);
+    if (e->h_tail) cudaFreeHost(e->h_tail);
     cudaFree(e->d_rowinfo); cudaFree(e->d_alias); cudaFree(e->d_starts);
     cudaFree(e->d_prefix); cudaFree(e->d_idbase); cudaFree(e->d_tally);
     delete e;
@@ -737,6 +741,11 @@ extern "C" int nrw_fluence_scores_host(nrw_engine* e, int32_t n_rows, int32_t n_
     w.start_id_base = start_id_base_host ? (const int64_t*)e->d_idbase : nullptr;
     w.walker_lo = walker_lo; w.walker_hi = walker_hi; w.seed = seed; w.nt = nt;
     w.sampler = NRW_SAMPLER_ALIAS; w.score = (int64_t*)tally;
+    // the start list goes first: these copies run while the host looks at the classes and plans the launch
+    CUDA_TRY(cudaMemcpyAsync(e->d_starts, start_nodes_host, (size_t)n_starts * 4, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(e->d_prefix, start_prefix_host, (size_t)(n_starts + 1) * 8, cudaMemcpyHostToDevice, st));
+    if (start_id_base_host)
+        CUDA_TRY(cudaMemcpyAsync(e->d_idbase, start_id_base_host, (size_t)n_starts * 8, cudaMemcpyHostToDevice, st));
     {   // weights of classes no row carries are free: if the used ones equal the class index, pass the
         // identity vector so that the walk takes the IDW kernel (walk_score.cuh)
         uint32_t present = 0;
@@ -749,20 +758,17 @@ extern "C" int nrw_fluence_scores_host(nrw_engine* e, int32_t n_rows, int32_t n_
     w.counters = (unsigned long long*)(tally + n_starts);
     w.reduce = reduce;
     if ((rc = stage_tables_host(e, &t, &w, rowinfo_host, alias_host, rowinfo_str_host, st))) return rc;
-    CUDA_TRY(cudaMemcpyAsync(e->d_starts, start_nodes_host, (size_t)n_starts * 4, cudaMemcpyHostToDevice, st));
-    CUDA_TRY(cudaMemcpyAsync(e->d_prefix, start_prefix_host, (size_t)(n_starts + 1) * 8, cudaMemcpyHostToDevice, st));
-    if (start_id_base_host)
-        CUDA_TRY(cudaMemcpyAsync(e->d_idbase, start_id_base_host, (size_t)n_starts * 8, cudaMemcpyHostToDevice, st));
     if ((rc = nrw_walk_philox(e, &t, &w, stream))) return rc;
     const long long* result = (reduce && reduce->world > 1) ? (const long long*)reduce->own_buf + reduce->out_offset : tally;
-    CUDA_TRY(cudaMemcpyAsync(score_host, result, (size_t)n_starts * 8, cudaMemcpyDeviceToHost, st));
     // counters (+ the exchange's status word: it follows the sums, after the pad word of an odd n -- n_tally is
-    // n_starts + 8, so the status sits at n_tally or n_tally + 1)
-    long long tail_host[NRW_N_COUNTERS + 2] = {0};
+    // n_starts + 8, so the status sits at n_tally or n_tally + 1) into the engine's PINNED tail buffer (a copy to a
+    // pageable stack array goes through the driver's staging path), then the scores
+    long long* tail_host = e->h_tail;
     const bool want_status = reduce && reduce->world > 1;
     if (counters_host || want_status)
         CUDA_TRY(cudaMemcpyAsync(tail_host, result + n_starts, (size_t)(NRW_N_COUNTERS + (want_status ? 2 : 0)) * 8,
                                  cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaMemcpyAsync(score_host, result, (size_t)n_starts * 8, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaStreamSynchronize(st));
     if (counters_host) memcpy(counters_host, tail_host, NRW_N_COUNTERS * sizeof(unsigned long long));
     if (want_status && tail_host[NRW_N_COUNTERS + (n_tally & 1)] != 0)

@@ -253,7 +253,7 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
             // step phase; a second loop back-edge cost 1 % -- 0.523 -> 0.517 ms on C5.)
             if (__all_sync(NRW_FULL_MASK, det_n != 0u && off < s_end_off)) {
                 const uint32_t lim = min(end, s_end_off);
-                const uint32_t k = (lim - cur - (uint32_t)lane + 31u) >> 5;
+                const uint32_t k = (lim - off + 31u) >> 5;         // (off = cur + lane here: every lane is dead)
                 x += det_w * k;
                 nst += k;
                 if constexpr (HIST) { nsink += det_hs * k; if (det_hn) [[unlikely]] atomicAdd(hist_s + det_tgt, k); }
