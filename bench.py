@@ -492,7 +492,7 @@ def run_ours(args):
         if rank == 0:
             line["c3"] = c3
     if rank == 0 and world == 1 and not args.no_extras:
-        line["resources"] = resource_leg(eng, tabs, starts, Mg, id_base, flush, steps_per_launch, kernel_ms, det_frac)
+        line["resources"] = resource_leg(eng, tabs, starts, Mg, id_base, flush, steps_per_launch, kernel_ms, det_frac, kernel=line["kernel"])
         line["roofline"]["mem"].update(
             smem_load_frac=line["resources"]["score_kernel"]["frac_of_smem_load_peak"],
             smem_atomic_frac_hist_mode=line["resources"]["hist_kernel"]["frac_of_smem_atomic_peak"])
@@ -698,7 +698,7 @@ def run_args_leg(rank, world, barrier):
                      "(import torch ~2 s, CUDA context ~1.2 s) is outside run() and not included"}
 
 
-def resource_leg(eng, tabs, starts, Mg, id_base, flush, steps_per_launch, kernel_ms, det_frac):
+def resource_leg(eng, tabs, starts, Mg, id_base, flush, steps_per_launch, kernel_ms, det_frac, kernel=""):
     """The memory/atomic rooflines named by BASELINE north_star: rates of the resources the walk
     touches, measured by micro-benchmarks at the walk's own launch geometry (nrw_microbench), next
     to the rates the walk kernels reach.  None of them is the binding resource (issue slots are)."""
@@ -710,9 +710,12 @@ def resource_leg(eng, tabs, starts, Mg, id_base, flush, steps_per_launch, kernel
     out = {"measured_peaks": peaks,
            "how": "nrw_microbench: one 1024-thread CTA per SM, random indices from a per-thread LCG, "
                   "dependent loads; best of 5 event-timed launches"}
-    # score kernel: two dependent shared-memory look-ups per drawn step (alias entry, row descriptor)
-    lds = 2.0 * steps_per_launch * (1.0 - det_frac) / (kernel_ms * 1e-3)
-    out["score_kernel"] = {"smem_loads_per_s": lds, "frac_of_smem_load_peak": lds / peaks["smem_random_load_8B_per_s"]}
+    # score kernel: shared-memory look-ups per drawn step -- two dependent ones with alias tables (alias entry, then
+    # the target's row descriptor), one with the structured draw (the descriptor alone)
+    per_step = 1.0 if "_str<" in kernel else 2.0
+    lds = per_step * steps_per_launch * (1.0 - det_frac) / (kernel_ms * 1e-3)
+    out["score_kernel"] = {"smem_loads_per_s": lds, "smem_loads_per_drawn_step": per_step,
+                           "frac_of_smem_load_peak": lds / peaks["smem_random_load_8B_per_s"]}
     # occupancy-histogram mode: one shared-memory atomic per walker-step (sink arrivals are counted in registers)
     hl, hres = eng.prepare_walk(tabs, starts, Mg, NT, seed=1, score=True, class_value=[0, 1, 0, 0],
                                 node_hist=True, start_id_base=id_base)
