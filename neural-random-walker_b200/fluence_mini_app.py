@@ -162,7 +162,7 @@ def run(args):
         if args['plot_results']:
             plot_results(rwSol, m['dirs'], m['space'], results_filename)
         t0 = time.perf_counter()
-        np.savetxt(results_filename, rwSol, delimiter=",")            # :446
+        mesh.save_array_csv(results_filename, rwSol)                  # :446 (np.savetxt's bytes)
         split['results_file_s'] = time.perf_counter() - t0
         rw_logger.info("Solution saved to {}".format(results_filename))
     if writer is not None:

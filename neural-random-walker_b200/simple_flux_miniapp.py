@@ -157,7 +157,7 @@ def run(args):
     if rank == 0:
         if args['plot_results']:
             plot_results(rwSol, maxT, args)
-        np.savetxt(results_filename, rwSol, delimiter=",")                    # :358
+        mesh.save_array_csv(results_filename, rwSol)                          # :358 (np.savetxt's bytes)
         rw_logger.info("Solution saved to {}".format(results_filename))
     return rwSol
 

@@ -429,3 +429,21 @@ def test_structured_rows_reproduce_every_alias_draw(c1_csr):
     a = int(stay[np.nonzero(np.diff(stay) == 1)[0][0]])
     at.rowinfo[[a, a + 1]] = at.rowinfo[[a + 1, a]]
     assert tables.structure_rows(at) is None
+
+
+def test_result_file_writer_is_np_savetxt_byte_for_byte(tmp_path):
+    """nrw.mesh.save_array_csv writes the result files of run() (fluence_mini_app.py:446, simple_flux_miniapp.py:358):
+    the bytes of np.savetxt(path, a, delimiter=','), for 1-D and 2-D arrays, signed zeros, denormals, inf and nan."""
+    from nrw import mesh
+    rng = np.random.default_rng(1)
+    cases = [rng.random(17), rng.random((5, 7)) - 0.5, rng.random((100, 100)) * 4, np.zeros((3, 1)),
+             np.arange(6).reshape(2, 3), np.zeros((0, 4)),
+             np.array([[0.0, -0.0, np.inf, -np.inf, np.nan, 1e-320, 1.7976931348623157e308]])]
+    for k, a in enumerate(cases):
+        p1, p2 = str(tmp_path / ("a%d.csv" % k)), str(tmp_path / ("b%d.csv" % k))
+        import warnings
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")                     # np.savetxt warns about the empty array
+            np.savetxt(p1, a, delimiter=",")
+            mesh.save_array_csv(p2, a)
+        assert open(p1, "rb").read() == open(p2, "rb").read(), (k, np.shape(a))
