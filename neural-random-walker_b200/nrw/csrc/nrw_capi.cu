@@ -581,6 +581,14 @@ static int make_plan(nrw_engine* e, const nrw_tables* t, const nrw_walk* w, Walk
         Z(TAB_SMEM) Z(TAB_HYB) Z(TAB_FAC)
 #undef Z
     }
+    // time-resolved counts in the CTA's own shared-memory histogram with plain atomics (small graphs over long windows:
+    // the 3-state chain of simple_flux over 1 002 steps), nothing else tallied, compact tables: the trimmed walk too
+    if (tl == TL_CNT_S && !p.cnt_match && tab == TAB_SMEM && w->nt >= 2 && !e->cfg.k1_general &&
+        32ll * (long long)w->nt < (1ll << 31)) {
+        while (p.range > 32 && p.range * (long long)w->nt >= (1ll << 31)) p.range = ((p.range / 2) / 32) * 32;
+        plan->fn = (const void*)walk_score_kernel<TAB_SMEM, true, false, 1, false, true, false, true>;
+        plan->name = "walk_count_smem<TAB_SMEM>";
+    }
     {   // guided range sizes (fetch_range, walk_philox.cuh).  NRW_RANGE_TAIL / NRW_TAIL_RANGES override
         // (0 ranges = one size)
         const long long warps = (long long)plan->grid * (plan->block / 32);

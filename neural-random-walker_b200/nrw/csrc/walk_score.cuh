@@ -88,11 +88,15 @@ __device__ __forceinline__ uint2 philox2x32_10_k0(uint32_t c0, uint32_t c1k, con
 // `same` where the pattern offset was, and  target = base + (coin <= p.str_thr ? slot : same)  -- the alias
 // draw's target for every (slot, coin), verified entry by entry on the host -- needs no alias look-up: one
 // shared-memory load per step instead of two dependent ones, and no alias patterns to stage.
-template <int TAB, bool IDW, bool DET, int CPS, bool HIST = false, bool CNT = false, bool STR = false>
+// CNTS (with CNT): the bins fit shared memory (p.sm_cnt, p.cnt_bins: small graphs over long windows -- the 3-state
+// chain of simple_flux_miniapp.py:174-203 over 1 002 steps): one plain shared-memory atomic per step into the CTA's
+// own histogram, merged into count_tn once; no path logic.
+template <int TAB, bool IDW, bool DET, int CPS, bool HIST = false, bool CNT = false, bool STR = false, bool CNTS = false>
 __global__ void __launch_bounds__(CPS == 1 ? 1024 : 768, CPS)
 walk_score_kernel(const __grid_constant__ WalkParams p) {
     static_assert(tab_compact(TAB), "compact alias tables only");
     static_assert(!CNT || (!DET && !HIST), "the count walk draws every step and tallies nothing else");
+    static_assert(!CNTS || CNT, "CNTS is a mode of the count walk");
     extern __shared__ __align__(16) unsigned char smem[];
     uint64_t* bar = reinterpret_cast<uint64_t*>(smem);
     const uint32_t rowinfo_a = smem_u32(smem + p.sm_rowinfo);      // 32-bit shared-window address of the descriptors
@@ -105,7 +109,10 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
         for (int i = tid; i < p.n_rows; i += (int)blockDim.x) hist_s[i] = 0u;
     int32_t* path_s = reinterpret_cast<int32_t*>(smem + p.sm_path);
     uint32_t* left_s = reinterpret_cast<uint32_t*>(smem + p.sm_left);
-    if constexpr (CNT) {
+    uint32_t* cnt_s = reinterpret_cast<uint32_t*>(smem + p.sm_cnt);
+    if constexpr (CNTS) {
+        for (int i = tid; i < p.cnt_bins; i += (int)blockDim.x) cnt_s[i] = 0u;
+    } else if constexpr (CNT) {
         for (int i = tid; i < p.n_starts * p.t_cap; i += (int)blockDim.x) path_s[i] = __ldg(p.cnt_path + i);
         for (int i = tid; i < p.n_starts * (p.t_cap + 1); i += (int)blockDim.x) left_s[i] = 0u;
     }
@@ -229,7 +236,7 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
         c0 = c0_base + off;
         ra = srow.x; rb = srow.y;
         t = t_init;
-        if constexpr (CNT) onpath = true;
+        if constexpr (CNT && !CNTS) onpath = true;
         if constexpr (DET) {
             x += det_w; nst += det_n;
             if constexpr (HIST) { nsink += det_hs; if (det_hn) [[unlikely]] atomicAdd(hist_s + det_tgt, 1u); }
@@ -339,7 +346,10 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
             ra = (STR && DET) ? sel : row.x; rb = row.y;
             if constexpr (CNT) {
                 const int k = (int)(knew & ROW_BASE_MASK);
-                if (tn < p.t_cap) {
+                if constexpr (CNTS) {
+                    if (tn < p.t_cap) atomicAdd(cnt_s + ((p.per_start ? s : 0) * p.t_cap + tn) * p.n_rows + k, 1u);
+                    else ++novf;
+                } else if (tn < p.t_cap) {
                     if (!(onpath && k == path_s[s * p.t_cap + tn])) {      // on the path: credited in the epilogue
                         if (onpath) leave_path(tn);
                         const long long gq = p.per_start ? s : 0;
@@ -436,9 +446,15 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) v3 += __shfl_xor_sync(NRW_FULL_MASK, v3, o);
         if (lane == 0 && p.counters && v3) atomicAdd(p.counters + 3, (unsigned long long)v3);
-        // walkers on the path at step tau = those that left it later: suffix sums of the leave-time histogram
         __syncthreads();
-        for (int sidx = tid; sidx < p.n_starts; sidx += (int)blockDim.x) {
+        if constexpr (CNTS) {
+            for (int i = tid; i < p.cnt_bins; i += (int)blockDim.x) {
+                const uint32_t h = cnt_s[i];
+                if (h) atomicAdd(p.count_tn + i, h);
+            }
+        }
+        // walkers on the path at step tau = those that left it later: suffix sums of the leave-time histogram
+        for (int sidx = tid; !CNTS && sidx < p.n_starts; sidx += (int)blockDim.x) {
             const long long gq = p.per_start ? sidx : 0;
             unsigned long long on = left_s[sidx * (p.t_cap + 1) + p.t_cap];
             for (int tau = p.t_cap - 1; tau >= 1; --tau) {

@@ -136,17 +136,27 @@ def test_hybrid_tables_bit_exact(engine, monkeypatch):
 
 
 def test_simple_flux_counts_smem_bit_exact(engine):
-    """2-state chain with absorption: time-resolved counts in the shared-memory tally with
-    __match_any_sync aggregation (every walker of a warp hits one of 3 bins per step)."""
+    """2-state chain with absorption (simple_flux_miniapp.py:174-203): time-resolved counts in the CTA's shared-memory
+    histogram, against the numpy port -- the trimmed count walk with plain atomics (long windows: the C3 shape), the
+    general kernel on the same launch (NRW_K1=general), and the general kernel's __match_any_sync aggregation (windows
+    of <= 256 steps); per-start and pooled bins, a window shorter than the walk (overflow counter), survivors."""
     from nrw import mesh
+    from nrw.engine import Engine
     from oracle import philox_port
     csr = mesh.csr_from_dense(mesh.build_simple_flux_dense(0.005, 8.0, 2.0), n_live=2)
     tabs = engine.upload(csr)
-    res = engine.walk(tabs, [0, 1], [5000, 3000], 300, 8, count_tn=True, t_cap=300, count_per_start=True)
-    assert ",16>" in res.kernel, res.kernel
-    port = philox_port.walk_port(csr, [0, 1], [5000, 3000], 300, 8, alias=tabs.alias_host, t_cap=300,
-                                 count_per_start=True)
-    _cmp(res, port, score=False, hist=False, count=True)
+    general = Engine(0, switches={"NRW_K1": "general"})
+    for nt, t_cap, per_start, want in ((300, 300, True, "walk_count_smem<"), (1002, 1002, False, "walk_count_smem<"),
+                                       (400, 290, True, "walk_count_smem<"), (12, 300, True, ",16>"),
+                                       (200, 200, True, ",16>")):
+        port = philox_port.walk_port(csr, [0, 1], [5000, 3000], nt, 8, alias=tabs.alias_host, t_cap=t_cap,
+                                     count_per_start=per_start)
+        res = engine.walk(tabs, [0, 1], [5000, 3000], nt, 8, count_tn=True, t_cap=t_cap, count_per_start=per_start)
+        assert want in res.kernel, res.kernel
+        _cmp(res, port, score=False, hist=False, count=True)
+        res_g = general.walk(tabs, [0, 1], [5000, 3000], nt, 8, count_tn=True, t_cap=t_cap, count_per_start=per_start)
+        assert ",16>" in res_g.kernel, res_g.kernel
+        _cmp(res_g, port, score=False, hist=False, count=True)
 
 
 def test_sharded_by_start_slices_equals_unsharded(engine, c1_csr):
