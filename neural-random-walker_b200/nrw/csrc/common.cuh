@@ -122,6 +122,11 @@ __device__ __forceinline__ uint2 lds64(uint32_t addr) {
     return v;
 }
 
+// fire-and-forget increment of a 32-bit shared-memory word at a 32-bit shared-window address
+__device__ __forceinline__ void red_shared_inc(uint32_t addr) {
+    asm volatile("red.shared.add.u32 [%0], 1;" ::"r"(addr) : "memory");
+}
+
 // ---- mbarrier + 1-D TMA bulk copy (global -> shared), SASS: UBLKCP ---------------------------
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));

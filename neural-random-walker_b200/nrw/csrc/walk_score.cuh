@@ -128,6 +128,10 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
 #pragma unroll
     for (int r = 0; r < 10; ++r) rk[r] = p.rk[r] + zz;
     const uint32_t t_fast = p.t_fast + zz, str_thr = p.str_thr + zz, str_n = p.str_n + zz;
+    // CNTS: steps below t_hot are inside the count window and before the last step of time (the common step)
+    const int t_hot = min(p.t_cap, p.t_last) + (int)zz;
+    const uint32_t n_rows_u = (uint32_t)p.n_rows + zz;
+    uint32_t cnt_a = 0;                          // CNTS: shared-window address of the lane's start's bins [t_cap][n_rows]
     const uint32_t lt_mask = lanemask_lt();
 
     // ---- the lane's walker --------------------------------------------------------------------------
@@ -214,6 +218,7 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
         rebase();
         if (off >= s_end_off) pass_wrap();       // the new start's ids wrapped before this lane's first one
         t_init = ((srow.x & ROW_N_MASK) == 0u) ? -1 : 0;       // started on the sink: an exit, no step
+        if constexpr (CNTS) cnt_a = smem_u32(cnt_s) + (uint32_t)((p.per_start ? s : 0) * p.t_cap * p.n_rows) * 4u;
         const uint32_t srow_w0 = srow.x;
         if constexpr (STR && DET) srow.x = row_off(srow_w0);    // the take hands a new walker its direction (step below)
         if constexpr (DET) {
@@ -347,6 +352,15 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
             if constexpr (CNT) {
                 const int k = (int)(knew & ROW_BASE_MASK);
                 if constexpr (CNTS) {
+                    if (tn < t_hot) [[likely]] {
+                        // the common step: inside the window, not the last step of time -- one shared-memory atomic on
+                        // the lane's start's bins, and the walk goes on unless the row is absorbing
+                        red_shared_inc(cnt_a + (((uint32_t)tn * n_rows_u + (uint32_t)k) << 2));
+                        ++nst;
+                        const bool absorbed = (row.x & ROW_N_MASK) == 0u;
+                        t = absorbed ? -1 : tn;
+                        return !absorbed;
+                    }
                     if (tn < p.t_cap) atomicAdd(cnt_s + ((p.per_start ? s : 0) * p.t_cap + tn) * p.n_rows + k, 1u);
                     else ++novf;
                 } else if (tn < p.t_cap) {
