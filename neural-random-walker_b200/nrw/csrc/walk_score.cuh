@@ -36,10 +36,36 @@ namespace nrw {
 
 // Descriptor of row k, where k may still carry the flag bits of the base it was formed from (bits 29..31 of w1:
 // common.cuh): in shared memory the 32-bit address arithmetic drops them ((k << 3) wraps), elsewhere they are masked.
+// The constants of fac_row (walk_philox.cuh) as VALUES the kernel computes once (walk_score_kernel adds p.zero to
+// each): read as plain kernel parameters they were re-loaded from the constant bank at every step -- six loads of
+// the ~30 instructions a factored descriptor costs.
+struct FacK {
+    uint32_t n_live, magic, shift, period, cells, exit_w0, exit_base;
+    uint32_t a_dir, a_tail, a_cls;               // 32-bit shared-window addresses of the three staged tables
+};
+__device__ __forceinline__ uint32_t lds32(uint32_t addr) {
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+    return v;
+}
+// fac_row with those values (same arithmetic, same result)
+__device__ __forceinline__ uint2 fac_row_k(const FacK& f, uint32_t k) {
+    if (k >= f.n_live) return lds64(f.a_tail + ((k - f.n_live) << 3));
+    const unsigned long long prod = (unsigned long long)k * f.magic;
+    const uint32_t j = __funnelshift_r((uint32_t)prod, (uint32_t)(prod >> 32), f.shift);   // k / period
+    const uint32_t i = k - j * f.period;
+    const uint2 d = lds64(f.a_dir + (i << 3));
+    const uint32_t jn = j + d.y;                                   // target cell (wraps when negative)
+    const uint32_t cls = (lds32(f.a_cls + ((k >> 4) << 2)) >> ((k & 15u) * 2u)) & 3u;
+    const bool leaves = jn >= f.cells;
+    return make_uint2((leaves ? f.exit_w0 : d.x) + cls * 0x28000000u,
+                      leaves ? f.exit_base : (jn * f.period) | 0x40000000u);
+}
+
 template <int TAB>
-__device__ __forceinline__ uint2 load_row2(const WalkParams& p, uint32_t rowinfo_a, uint32_t k) {
+__device__ __forceinline__ uint2 load_row2(const WalkParams& p, uint32_t rowinfo_a, uint32_t k, const FacK& f) {
     if constexpr (TAB == TAB_SMEM) return lds64(rowinfo_a + (k << 3));
-    else if constexpr (TAB == TAB_FAC) return fac_row(p, (int)(k & ROW_BASE_MASK));
+    else if constexpr (TAB == TAB_FAC) return fac_row_k(f, k & ROW_BASE_MASK);
     else return __ldg(reinterpret_cast<const uint2*>(p.rowinfo) + (k & ROW_BASE_MASK));
 }
 
@@ -132,6 +158,16 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
     const int t_hot = min(p.t_cap, p.t_last) + (int)zz;
     const uint32_t n_rows_u = (uint32_t)p.n_rows + zz;
     uint32_t cnt_a = 0;                          // CNTS: shared-window address of the lane's start's bins [t_cap][n_rows]
+    uint32_t path_a = 0, left_a = 0;             // CNT: shared-window addresses of the lane's start's path / leave histogram
+    uint32_t* cnt_g = nullptr;                   // CNT: the lane's start's bins in global memory
+    FacK fk = {};
+    if constexpr (TAB == TAB_FAC) {
+        fk.n_live = (uint32_t)p.n_live + zz; fk.magic = p.fac_magic + zz; fk.shift = (uint32_t)p.fac_shift + zz;
+        fk.period = (uint32_t)p.fac_period + zz; fk.cells = (uint32_t)p.fac_cells + zz;
+        fk.exit_w0 = p.fac_exit_w0 + zz; fk.exit_base = p.fac_exit_base + zz;
+        fk.a_dir = smem_u32(smem + p.sm_fdir) + zz; fk.a_tail = smem_u32(smem + p.sm_ftail) + zz;
+        fk.a_cls = smem_u32(smem + p.sm_fcls) + zz;
+    }
     const uint32_t lt_mask = lanemask_lt();
 
     // ---- the lane's walker --------------------------------------------------------------------------
@@ -213,12 +249,17 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
             s_lo = __ldg(p.start_prefix + s);
             s_end = __ldg(p.start_prefix + s + 1);
         }
-        srow = load_row2<TAB>(p, rowinfo_a, (uint32_t)__ldg(p.start_nodes + s));
+        srow = load_row2<TAB>(p, rowinfo_a, (uint32_t)__ldg(p.start_nodes + s), fk);
         sid_base = rbase + (p.start_id_base ? (__ldg(p.start_id_base + s) - s_lo) : 0ll);
         rebase();
         if (off >= s_end_off) pass_wrap();       // the new start's ids wrapped before this lane's first one
         t_init = ((srow.x & ROW_N_MASK) == 0u) ? -1 : 0;       // started on the sink: an exit, no step
         if constexpr (CNTS) cnt_a = smem_u32(cnt_s) + (uint32_t)((p.per_start ? s : 0) * p.t_cap * p.n_rows) * 4u;
+        if constexpr (CNT && !CNTS) {
+            path_a = smem_u32(path_s + s * p.t_cap);
+            left_a = smem_u32(left_s + s * (p.t_cap + 1));
+            cnt_g = p.count_tn + (long long)(p.per_start ? s : 0) * p.t_cap * (long long)p.n_rows;
+        }
         const uint32_t srow_w0 = srow.x;
         if constexpr (STR && DET) srow.x = row_off(srow_w0);    // the take hands a new walker its direction (step below)
         if constexpr (DET) {
@@ -347,7 +388,7 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
                 const uint2 e = alias_s[row_off(ra) + slot];
                 knew = rb + ((coin <= e.x) ? (e.y & 0xffffu) : (e.y >> 16));
             }
-            const uint2 row = load_row2<TAB>(p, rowinfo_a, knew);
+            const uint2 row = load_row2<TAB>(p, rowinfo_a, knew, fk);
             ra = (STR && DET) ? sel : row.x; rb = row.y;
             if constexpr (CNT) {
                 const int k = (int)(knew & ROW_BASE_MASK);
@@ -363,6 +404,22 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
                     }
                     if (tn < p.t_cap) atomicAdd(cnt_s + ((p.per_start ? s : 0) * p.t_cap + tn) * p.n_rows + k, 1u);
                     else ++novf;
+                } else if (tn < t_hot) {
+                    // (NO [[likely]] on this line: with the attribute on an `else if` that continues an `if constexpr`
+                    // chain, nvcc 12.9 dropped the statement that FOLLOWS the chain -- the `++nst` below -- from the
+                    // instantiation in which this branch is discarded; seen in the PTX, caught by the port's step count)
+                    // the common step (inside the window, before the last step of time), with the lane's start's
+                    // bases kept per lane: a walker on its start's path is credited in the epilogue, one that leaves
+                    // it records the step, steps off the path go to their bins
+                    if (!(onpath && (uint32_t)k == lds32(path_a + ((uint32_t)tn << 2)))) {
+                        if (onpath) { red_shared_inc(left_a + ((uint32_t)tn << 2)); onpath = false; }
+                        atomicAdd(cnt_g + ((size_t)(uint32_t)tn * n_rows_u + (uint32_t)k), 1u);
+                    }
+                    ++nst;
+                    const bool absorbed = (row.x & ROW_N_MASK) == 0u;
+                    if (absorbed && onpath) { red_shared_inc(left_a + ((uint32_t)(tn + 1) << 2)); onpath = false; }
+                    t = absorbed ? -1 : tn;
+                    return !absorbed;
                 } else if (tn < p.t_cap) {
                     if (!(onpath && k == path_s[s * p.t_cap + tn])) {      // on the path: credited in the epilogue
                         if (onpath) leave_path(tn);
