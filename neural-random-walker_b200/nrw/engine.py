@@ -83,7 +83,8 @@ _lib = None
 EXPORTS = ("nrw_abi_version", "nrw_last_error", "nrw_create", "nrw_destroy", "nrw_device_info", "nrw_engine_config",
            "nrw_build_cum", "nrw_walk_philox", "nrw_walk_philox_plan", "nrw_walk_replay",
            "nrw_assemble_events", "nrw_expand_events", "nrw_expand_counts",
-           "nrw_fluence_scores_host", "nrw_fluence_scores_host_static", "nrw_microbench", "nrw_p2p_allreduce_i64", "nrw_guided_phases")
+           "nrw_fluence_scores_host", "nrw_fluence_scores_host_static", "nrw_microbench", "nrw_p2p_allreduce_i64", "nrw_guided_phases",
+           "nrw_format_csv_e18")
 
 
 def load_library():
@@ -119,6 +120,7 @@ def load_library():
     lib.nrw_microbench.argtypes = [vp, i32, i32, i32, vp, vp, vp, vp]
     lib.nrw_p2p_allreduce_i64.argtypes = [vp, vp, vp, i64, i64, i64, i64, i32, i32, u64, vp, vp]
     lib.nrw_guided_phases.argtypes = [i64, i64, i64, i64, i64, vp, vp, vp, C.POINTER(i32)]
+    lib.nrw_format_csv_e18.argtypes = [vp, i64, i64, vp, i64, C.POINTER(i64), i32]
     for name in EXPORTS:
         fn = getattr(lib, name)
         if name != "nrw_last_error":

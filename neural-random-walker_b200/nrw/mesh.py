@@ -253,9 +253,32 @@ def save_array_csv(path: str, a) -> None:
         np.savetxt(path, a, delimiter=",")
         return
     ncols = 1 if a.ndim == 1 else a.shape[1]
-    row = ",".join(["%.18e"] * ncols) + "\n"
-    with open(path, "w") as f:
-        f.write((row * (a.size // ncols)) % tuple(a.ravel().tolist()))
+    nrows = a.size // ncols
+    text = _format_csv_native(np.ascontiguousarray(a), nrows, ncols) if a.size >= 2048 else None
+    if text is None:                         # small arrays, or libnrw.so not built: one C-level format call in Python
+        row = ",".join(["%.18e"] * ncols) + "\n"
+        text = ((row * nrows) % tuple(a.ravel().tolist())).encode("ascii")
+    with open(path, "wb") as f:
+        f.write(text)
+
+
+def _format_csv_native(a: np.ndarray, nrows: int, ncols: int):
+    """The same text from libnrw.so (nrw_format_csv_e18: the rows converted by a few host threads), or None when the
+    library is not there.  A correctly rounded 19-digit conversion costs ~0.3 us per value in any libc and in CPython;
+    on the 10 000-cell mesh that was 2.6 ms of a 5.9 ms run(args)."""
+    import ctypes as C
+    try:
+        from .engine import load_library
+        lib = load_library()
+    except Exception:
+        return None
+    cap = nrows * ncols * 28
+    out = C.create_string_buffer(cap)
+    n = C.c_int64(0)
+    threads = max(1, min(8, (os.cpu_count() or 1)))
+    if lib.nrw_format_csv_e18(C.c_void_p(a.ctypes.data), nrows, ncols, out, cap, C.byref(n), threads) != 0:
+        return None
+    return out.raw[:n.value]
 
 
 def save_matrix_npz(path: str, csr: TransitionCSR) -> None:

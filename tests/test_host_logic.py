@@ -436,7 +436,11 @@ def test_result_file_writer_is_np_savetxt_byte_for_byte(tmp_path):
     the bytes of np.savetxt(path, a, delimiter=','), for 1-D and 2-D arrays, signed zeros, denormals, inf and nan."""
     from nrw import mesh
     rng = np.random.default_rng(1)
-    cases = [rng.random(17), rng.random((5, 7)) - 0.5, rng.random((100, 100)) * 4, np.zeros((3, 1)),
+    big = (rng.random((300, 37)) - 0.5) * 10.0 ** rng.integers(-300, 300, size=(300, 37))    # through libnrw.so
+    big[5, 5], big[6, 0], big[7, 36], big[8, 1], big[9, 9] = np.nan, np.inf, -np.inf, -0.0, 5e-324
+    big[10, 3] = -np.nan
+    cases = [rng.random(17), rng.random((5, 7)) - 0.5, rng.random((100, 100)) * 4, np.zeros((3, 1)), big, big[:, 0],
+             rng.random(5000),
              np.arange(6).reshape(2, 3), np.zeros((0, 4)),
              np.array([[0.0, -0.0, np.inf, -np.inf, np.nan, 1e-320, 1.7976931348623157e308]])]
     for k, a in enumerate(cases):
