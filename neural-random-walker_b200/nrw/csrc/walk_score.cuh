@@ -123,6 +123,8 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
     static_assert(tab_compact(TAB), "compact alias tables only");
     static_assert(!CNT || (!DET && !HIST), "the count walk draws every step and tallies nothing else");
     static_assert(!CNTS || CNT, "CNTS is a mode of the count walk");
+    // FACJ: factored descriptors under the structured draw with deterministic exits -- the walker carries its cell
+    constexpr bool FACJ = TAB == TAB_FAC && STR && DET;
     extern __shared__ __align__(16) unsigned char smem[];
     uint64_t* bar = reinterpret_cast<uint64_t*>(smem);
     const uint32_t rowinfo_a = smem_u32(smem + p.sm_rowinfo);      // 32-bit shared-window address of the descriptors
@@ -260,8 +262,10 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
             left_a = smem_u32(left_s + s * (p.t_cap + 1));
             cnt_g = p.count_tn + (long long)(p.per_start ? s : 0) * p.t_cap * (long long)p.n_rows;
         }
-        const uint32_t srow_w0 = srow.x;
+        const uint32_t srow_w0 = srow.x, srow_w1 = srow.y;
         if constexpr (STR && DET) srow.x = row_off(srow_w0);    // the take hands a new walker its direction (step below)
+        // ... and on factored descriptors the CELL its start row points to instead of that cell's first row (FACJ, step)
+        if constexpr (FACJ) srow.y = (uint32_t)(((unsigned long long)row_base(srow_w1) * fk.magic) >> fk.shift);
         if constexpr (DET) {
             // a start whose single successor is absorbing: every walker takes that one step (t = 1)
             // and exits; no draw can change it, so the take accounts for it and the lane stays free
@@ -270,7 +274,7 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
             det_w = (det && t_last >= 2) ? weight_of(row_detcls(srow_w0)) : 0u;   // t = nt-1 is outside the sum
             if (det) t_init = -1;
             if constexpr (HIST) {
-                det_tgt = det ? det_target(srow_w0, srow.y) : 0;
+                det_tgt = det ? det_target(srow_w0, srow_w1) : 0;
                 const bool in_sum = det && t_last >= 2;
                 det_hs = (in_sum && det_tgt == sink_row) ? 1u : 0u;
                 det_hn = (in_sum && det_tgt != sink_row) ? 1u : 0u;
@@ -375,6 +379,24 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
             // target row; rb still carries its flag bits, which the descriptor look-up drops (load_row2)
             uint32_t knew;
             uint32_t sel = 0;
+            uint2 row;
+            if constexpr (FACJ) {
+                // Factored descriptors, structured draw: the walker carries (direction, cell) -- rb is the CELL the row it
+                // stands on points to, i.e. the cell of the row it is about to land on.  New row = (sel, rb): its index
+                // needs no division (fac_row derives direction and cell from the row index: four instructions), and
+                // the first row of its target cell is never needed -- only the target cell itself.  Same descriptor
+                // words as fac_row_k for every live row (flags, inc, sinc); rows >= n_live (the sink) are never landed on
+                // by a draw (a stay row's targets are the rows of a live cell).
+                sel = (coin <= str_thr) ? slot : ra;
+                const uint2 d = lds64(fk.a_dir + (sel << 3));
+                knew = rb * fk.period + sel;
+                const uint32_t jn = rb + d.y;                          // the new row's target cell (wraps when negative)
+                const uint32_t cls = (lds32(fk.a_cls + ((knew >> 4) << 2)) >> ((knew & 15u) * 2u)) & 3u;
+                const bool leaves = jn >= fk.cells;
+                row.x = (leaves ? fk.exit_w0 : d.x) + cls * 0x28000000u;
+                row.y = leaves ? fk.exit_base : 0x40000000u;           // flag bits (sinc, detlast); plus the exit row's base
+                ra = sel; rb = jn;
+            } else {
             if constexpr (STR && DET) {
                 // ra is the walker's DIRECTION, not its descriptor word: the offset a walker was sent to IS the `same`
                 // of the row it landed on (row = first row of the cell + direction; tables.structure_rows verifies it
@@ -388,8 +410,9 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
                 const uint2 e = alias_s[row_off(ra) + slot];
                 knew = rb + ((coin <= e.x) ? (e.y & 0xffffu) : (e.y >> 16));
             }
-            const uint2 row = load_row2<TAB>(p, rowinfo_a, knew, fk);
+            row = load_row2<TAB>(p, rowinfo_a, knew, fk);
             ra = (STR && DET) ? sel : row.x; rb = row.y;
+            }
             if constexpr (CNT) {
                 const int k = (int)(knew & ROW_BASE_MASK);
                 if constexpr (CNTS) {
