@@ -302,7 +302,19 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
         // hot: the range holds an id for every dead lane and (DET) at least one lane is walking -- one test, one branch
         if (ncur <= end && (!DET || need != NRW_FULL_MASK)) [[likely]] {
             cur = ncur;
-            if (dead) take(off);
+            if constexpr (!HIST && !CNT) {
+                // the take as selects behind ONE divergent branch (the cold change of start): two reconvergence points
+                // and a branch less than `if (dead) take(off)`, all lanes in step (C5 0.403 -> 0.4015 ms; with every
+                // step drawn, where every iteration refills most lanes, 0.674 -> 0.640 ms).  Round 1 had measured the
+                // opposite (+1 %) on a loop with 134 instructions; on this one the branches weigh more.
+                if (dead && off >= s_end_off) [[unlikely]] next_start(off);
+                c0 = dead ? c0_base + off : c0;
+                ra = dead ? srow.x : ra; rb = dead ? srow.y : rb;
+                t = dead ? t_init : t;
+                if constexpr (DET) { x += dead ? det_w : 0u; nst += dead ? det_n : 0u; }
+            } else {
+                if (dead) take(off);
+            }
         } else if (ncur <= end) {
             // DET: the whole warp is idle.  Inside a deterministic-exit start (nothing there ever enters the step
             // phase) it accounts for every id the range and the start still hold in one go, lane L standing for ids
@@ -342,8 +354,7 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
         }
 
         // refilled and surviving lanes step together (without this the compiler sends the two groups through
-        // the step code separately: 0.52 -> 0.83 ms; turning the take into selects instead of a divergent block
-        // was measured too and is 1 % slower)
+        // the step code separately: 0.52 -> 0.83 ms)
         __syncwarp();
 
         // ---- one model step (fluence_mini_app.py:243-245 + the fused :428-434) -----------------------
