@@ -302,7 +302,10 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
         // hot: the range holds an id for every dead lane and (DET) at least one lane is walking -- one test, one branch
         if (ncur <= end && (!DET || need != NRW_FULL_MASK)) [[likely]] {
             cur = ncur;
-            if constexpr (!HIST && !CNT) {
+            if constexpr (!HIST && !CNT && TAB == TAB_SMEM) {
+                // (Tables in shared memory = coarse meshes = short walks: most lanes are refilled in every iteration.
+                // On the refined mesh walkers live 17 steps, most iterations refill nobody and the divergent block
+                // below is skipped altogether: there the selects cost 5 % -- 4.81e11 -> 4.58e11 -- and are not used.)
                 // the take as selects behind ONE divergent branch (the cold change of start): two reconvergence points
                 // and a branch less than `if (dead) take(off)`, all lanes in step (C5 0.403 -> 0.4015 ms; with every
                 // step drawn, where every iteration refills most lanes, 0.674 -> 0.640 ms).  Round 1 had measured the
