@@ -520,6 +520,22 @@ walk_score_kernel(const __grid_constant__ WalkParams p) {
             // "^ key ^ c1" is one three-input LOP3
             const uint2 r = philox2x32_10_k0(c0, chi_base ^ (uint32_t)(t + 1), rk);
             const unsigned long long va = (unsigned long long)r.x * rlen(ra);
+            if constexpr (!decltype(near_c)::value && STR && DET && IDW && TAB == TAB_SMEM && !HIST && !CNT) {
+                // The flagship pair with its second step written out: draw, choice and (clamped) address of the second
+                // step do not depend on the first step's look-up, so they are issued while that look-up is in flight
+                // (the loop waits on fixed latencies more than on anything else: DESIGN.md section 3).  Lanes whose
+                // walker ended in the first step look up row 0 and discard it.  C5 0.4005 -> 0.3935 ms.
+                const bool a1 = step(near_c, (uint32_t)(va >> 32), (uint32_t)va);
+                const unsigned long long vb = (unsigned long long)r.y * str_n;
+                const uint32_t sel = ((uint32_t)vb <= str_thr) ? (uint32_t)(vb >> 32) : ra;
+                const uint2 row = lds64(rowinfo_a + ((a1 ? rb + sel : 0u) << 3));
+                if (a1) {
+                    x += row_inc(row.x); nst += row_sinc(row.y);
+                    ra = sel; rb = row.y;
+                    t = (row.x & ROW_TERM) ? -1 : t + 1;
+                }
+                return;
+            }
             if (step(near_c, (uint32_t)(va >> 32), (uint32_t)va)) {
                 const unsigned long long vb = (unsigned long long)r.y * rlen(ra);
                 step(near_c, (uint32_t)(vb >> 32), (uint32_t)vb);
