@@ -12,8 +12,15 @@
 //     node finds it by interpolation (locate_start) instead of bisection;
 //   * paired draws (common.cuh): a refill is followed by TWO steps sharing one Philox call -- lanes
 //     are only refilled at the top of the pair, so every live lane is at an even step;
-//   * the Philox round keys come from the kernel parameters (constant-bank operands), not from
-//     uniform-register arithmetic repeated every iteration;
+//   * the loop's constants (Philox round keys, threshold, row length, end-of-time bound) are read as p.x + p.zero:
+//     computed values stay in registers, plain constant-bank operands were re-loaded in every iteration;
+//   * STR (nrw_tables.rowinfo_str / str_thresh / str_n): on fluence matrices the alias tables have a closed form --
+//     target = base + (coin <= T ? slot : same) -- so a step is ONE shared-memory look-up; with DET the row length is
+//     a launch constant and the walker carries its direction (and, on factored descriptors, its cell: FACJ);
+//   * one unsigned test at the head of a step pair says "the lane holds a walker" and "neither step of the pair can
+//     reach the last two steps of time"; the pair near the end of time is a cold copy with the tests; the flagship
+//     pair has its second step written out, so that its draw, choice and address are issued while the first step's
+//     look-up is in flight; with the tables in shared memory the take is a run of selects behind one cold branch;
 //   * the score is a per-lane running sum over the lane's walkers (flushed when the start node
 //     changes and at every range fetch); the common step is branch-free: what arriving on a row adds to score
 //     and step count sits in the top bits of its descriptor (one shift-add each), no separate path for lanes

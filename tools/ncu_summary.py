@@ -59,8 +59,18 @@ def plan_name(ncu_name):
     return ncu_name
 
 
+def strip_comments(src: str) -> str:
+    """C++ source without its comments and with runs of white space collapsed (string literals kept as they are):
+    what the digest below hashes, so that a comment or a re-wrapped line does not invalidate a capture."""
+    import re
+    pat = re.compile(r'"(?:\\.|[^"\\])*"|\'(?:\\.|[^\'\\])*\'|//[^\n]*|/\*.*?\*/', re.S)
+    code = pat.sub(lambda m: m.group(0) if m.group(0)[0] in "\"'" else " ", src)
+    return re.sub(r"\s+", " ", code).strip()
+
+
 def csrc_sha256():
-    """Digest of the CUDA sources the library is built from: bench.py refuses a capture of other kernel code."""
+    """Digest of the CUDA sources the library is built from -- their CODE: comments and white space are left out --
+    so that bench.py refuses a capture of other kernel code."""
     import glob
     import hashlib
     import os
@@ -68,7 +78,7 @@ def csrc_sha256():
     h = hashlib.sha256()
     for f in sorted(glob.glob(os.path.join(root, "*.cu")) + glob.glob(os.path.join(root, "*.cuh"))):
         h.update(os.path.basename(f).encode())
-        h.update(open(f, "rb").read())
+        h.update(strip_comments(open(f, "r", encoding="utf-8", errors="replace").read()).encode())
     return h.hexdigest()
 
 
