@@ -451,3 +451,37 @@ def test_result_file_writer_is_np_savetxt_byte_for_byte(tmp_path):
             np.savetxt(p1, a, delimiter=",")
             mesh.save_array_csv(p2, a)
         assert open(p1, "rb").read() == open(p2, "rb").read(), (k, np.shape(a))
+
+
+def test_format_csv_entry_argument_checks():
+    """nrw_format_csv_e18 (host only): too small an output buffer is NRW_ENOSPC with both sizes in the message, bad
+    arguments are NRW_EINVAL, one thread and many threads give the same bytes."""
+    import ctypes as C
+    from nrw.engine import load_library
+    lib = load_library()
+    a = np.ascontiguousarray(np.random.default_rng(3).standard_normal((64, 40)))
+    out = C.create_string_buffer(a.size * 28)
+    n = C.c_int64(0)
+    assert lib.nrw_format_csv_e18(C.c_void_p(a.ctypes.data), 64, 40, out, 100, C.byref(n), 4) == -3
+    assert "100" in lib.nrw_last_error().decode()
+    assert lib.nrw_format_csv_e18(None, 64, 40, out, a.size * 28, C.byref(n), 4) == -1
+    assert lib.nrw_format_csv_e18(C.c_void_p(a.ctypes.data), 64, 0, out, a.size * 28, C.byref(n), 4) == -1
+    texts = []
+    for threads in (1, 3, 64):
+        assert lib.nrw_format_csv_e18(C.c_void_p(a.ctypes.data), 64, 40, out, a.size * 28, C.byref(n), threads) == 0
+        texts.append(out.raw[:n.value])
+    assert texts[0] == texts[1] == texts[2]
+    want = "".join(",".join("%.18e" % v for v in row) + "\n" for row in a).encode()
+    assert texts[0] == want
+
+
+def test_capture_digest_ignores_comments_and_white_space():
+    """tools/ncu_summary.csrc_sha256 hashes the CODE of the CUDA sources (bench.py refuses a capture of other kernel
+    code, not of a re-worded comment): strip_comments drops // and /* */ comments and collapses white space, and
+    leaves string and character literals alone."""
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    from ncu_summary import strip_comments
+    src = 'int a = 1; // c1\n/* block\n comment */ const char* s = "// kept /* too */";\tchar c = \'"\';   // tail\nasm("x;" :: "r"(a));'
+    assert strip_comments(src) == 'int a = 1; const char* s = "// kept /* too */"; char c = \'"\'; asm("x;" :: "r"(a));'
+    assert strip_comments("a  =\n\n b ;") == strip_comments("a = b ; // same code")
