@@ -191,13 +191,15 @@ def structure_rows(at: "AliasTables"):
     # (row, slot) whose target is such a row.
     base = (ri[:, 1] & np.uint32(ROW_BASE_MASK)).astype(np.int64)
     src = np.nonzero(draws)[0]
-    if len(src):
-        tgt = (base[src][:, None] + np.arange(n_draw, dtype=np.int64)[None, :]).reshape(-1)
-        slot = np.tile(np.arange(n_draw, dtype=np.int64), len(src))
+    slots = np.arange(n_draw, dtype=np.int64)
+    same64 = same.astype(np.int64)
+    block = max(1, (1 << 22) // max(n_draw, 1))                           # ~4 M (row, slot) pairs at a time
+    for lo in range(0, len(src), block):
+        tgt = base[src[lo:lo + block]][:, None] + slots[None, :]
         if tgt.max() >= len(w0):
             return None
         onward = draws[tgt]
-        if not np.array_equal(same[tgt[onward]].astype(np.int64), slot[onward]):
+        if not np.array_equal(same64[tgt][onward], np.broadcast_to(slots[None, :], tgt.shape)[onward]):
             return None
     out = ri.copy()
     out[:, 0] = (w0 & ~np.uint32(0x7FFF)) | same
