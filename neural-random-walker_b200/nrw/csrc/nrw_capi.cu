@@ -2,6 +2,7 @@
 // no torch types; errors are returned, never thrown.
 #include "../../../include/nrw.h"
 
+#include <clocale>
 #include <cstdarg>
 #include <cstdio>
 #include <algorithm>
@@ -962,6 +963,11 @@ static size_t format_rows_e18(const double* a, int64_t r0, int64_t r1, int64_t n
 extern "C" int nrw_format_csv_e18(const double* a, int64_t nrows, int64_t ncols, char* out, int64_t cap,
                                   int64_t* len, int32_t n_threads) {
     if (!a || !out || !len || nrows < 0 || ncols <= 0) return fail(NRW_EINVAL, "nrw_format_csv_e18: bad argument");
+    {   // np.savetxt's text does not depend on the locale; snprintf's decimal point does
+        const struct lconv* lc = localeconv();
+        if (lc && lc->decimal_point && strcmp(lc->decimal_point, ".") != 0)
+            return fail(NRW_EINVAL, "nrw_format_csv_e18: LC_NUMERIC has decimal point '%s'; format in the caller", lc->decimal_point);
+    }
     const int64_t per_value = 28;                                      // -d.{18}e+XXX (26) + delimiter, rounded up
     if (cap < nrows * ncols * per_value) return fail(NRW_ENOSPC, "nrw_format_csv_e18: out needs %lld bytes, has %lld",
                                                      (long long)(nrows * ncols * per_value), (long long)cap);
